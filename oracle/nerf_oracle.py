@@ -1,0 +1,310 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement (the "oracle") of the reference hot path.
+
+This file restates, in plain fp32 torch-on-CPU / float64 numpy, the algorithm of
+rkin100g/Nerf-Replication's ``Renderer.render`` + ``Network.forward`` + the training step.  It is
+the checker for the CUDA engine: only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import it.  The product path never does.
+
+Parity status: PINNED.  ``oracle/make_golden.py`` (run in the build container, where the reference
+tree exists) executes the unmodified reference (``oracle/ref_loader.py``) and checks every tap of
+this restatement against it bit-for-bit on CPU, then writes ``tests/golden/*.npz``;
+``tests/test_oracle.py`` re-checks this file against those goldens everywhere.
+
+Citations are ``file:line`` relative to the reference root.
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+# ----------------------------------------------------------------------------------------------
+# Constants of the synthetic "lego-shaped" camera.
+CAMERA_ANGLE_X = 0.6911112070083618
+ORBIT_RADIUS = 4.031128874
+NEAR, FAR = 2.0, 6.0  # volume_renderer.py:27 (defaults never overridden by render, :306-308)
+
+# Parameter order = nn.Module registration order in NeRF.__init__ (network.py:22-47).
+LAYER_SHAPES = (
+    [("pts_linears.0", 256, 63)]
+    + [("pts_linears.%d" % i, 256, 256) for i in range(1, 5)]
+    + [("pts_linears.5", 256, 319), ("pts_linears.6", 256, 256), ("pts_linears.7", 256, 256)]
+    + [("views_linears.0", 128, 283), ("feature_linear", 256, 256), ("alpha_linear", 1, 256),
+       ("rgb_linear", 3, 128)]
+)
+PARAMS_PER_NET = sum(o * i + o for _, o, i in LAYER_SHAPES)  # 595 844
+FLOP_PER_EVAL = 2 * sum(o * i for _, o, i in LAYER_SHAPES)   # 1 186 816
+
+
+def state_dict_keys():
+    keys = []
+    for net in ("model", "model_fine"):
+        for name, _, _ in LAYER_SHAPES:
+            keys += ["%s.%s.weight" % (net, name), "%s.%s.bias" % (net, name)]
+    return keys
+
+
+def init_state_dict(seed=0, sharp=False):
+    """``torch.manual_seed(seed); Network()`` restated: nn.Linear default init in registration
+    order, coarse net then fine net (network.py:144-161).  ``sharp`` = the second, more
+    discriminating weight set of SURVEY.md section 8d (alpha_linear.weight x40, bias +0.5)."""
+    torch.manual_seed(seed)
+    sd = {}
+    for net in ("model", "model_fine"):
+        for name, o, i in LAYER_SHAPES:
+            lin = torch.nn.Linear(i, o)
+            sd["%s.%s.weight" % (net, name)] = lin.weight.detach().clone()
+            sd["%s.%s.bias" % (net, name)] = lin.bias.detach().clone()
+    if sharp:
+        for net in ("model", "model_fine"):
+            sd[net + ".alpha_linear.weight"] = sd[net + ".alpha_linear.weight"] * 40.0
+            sd[net + ".alpha_linear.bias"] = sd[net + ".alpha_linear.bias"] + 0.5
+    return sd
+
+
+def round_weights_bf16(sd):
+    """bf16-representable copy (kept as fp32) -- the oracle for the bf16 engine mode."""
+    return {k: (v.to(torch.bfloat16).to(torch.float32) if k.endswith("weight") else v.clone())
+            for k, v in sd.items()}
+
+
+# ----------------------------------------------------------------------------------------------
+# a-B  get_rays  (src/datasets/nerf/blender.py:95-127), float64 numpy -> float32
+def lego_pose(k=0, n_views=8, elevation_deg=30.0, radius=ORBIT_RADIUS):
+    """Camera-to-world 4x4 (float64), camera on a sphere looking at the origin, OpenGL/Blender
+    convention (-z forward, +y up) as blender.py:122-127 expects."""
+    az = 2.0 * math.pi * k / n_views
+    el = math.radians(elevation_deg)
+    eye = radius * np.array([math.cos(el) * math.cos(az), math.cos(el) * math.sin(az), math.sin(el)])
+    fwd = -eye / np.linalg.norm(eye)            # viewing direction
+    up_w = np.array([0.0, 0.0, 1.0])
+    right = np.cross(fwd, up_w)
+    right /= np.linalg.norm(right)
+    up = np.cross(right, fwd)
+    c2w = np.eye(4)
+    c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3] = right, up, -fwd, eye
+    return c2w
+
+
+def focal_from_fov(W, camera_angle_x=CAMERA_ANGLE_X):
+    return W / (2.0 * math.tan(camera_angle_x / 2.0))   # blender.py:102
+
+
+def get_rays_np(c2w, H, W, pixel_ids=None, camera_angle_x=CAMERA_ANGLE_X):
+    """blender.py:102-127.  Integer pixel coordinates (no +0.5), unit-length rays_d, float64
+    arithmetic; the DataLoader collate turns them into float32 (blender.py:163-169)."""
+    f = focal_from_fov(W, camera_angle_x)
+    cx, cy = W / 2, H / 2
+    if pixel_ids is None:
+        pixel_ids = np.arange(H * W)
+    u = (pixel_ids % W).astype(np.float64)     # :109 / meshgrid :114-115 (row-major)
+    v = (pixel_ids // W).astype(np.float64)
+    dirs = np.stack([(u - cx) / f, -(v - cy) / f, -np.ones_like(u)], axis=-1)   # :122
+    rays_d = (np.asarray(c2w)[:3, :3] @ dirs.T).T                               # :125
+    rays_d = rays_d / np.linalg.norm(rays_d, axis=-1, keepdims=True)           # :126
+    rays_o = np.broadcast_to(np.asarray(c2w)[:3, 3], rays_d.shape).copy()       # :127
+    return rays_o.astype(np.float32), rays_d.astype(np.float32)
+
+
+# ----------------------------------------------------------------------------------------------
+# a-C  stratified sampling (volume_renderer.py:27-65)
+def stratified_t(n_rays, n_samples, jitter=None, near=NEAR, far=FAR):
+    t_lin = torch.linspace(near, far, n_samples)                   # :44
+    t = t_lin.unsqueeze(0).expand(n_rays, n_samples).clone()       # :45
+    if jitter is not None:                                         # perturb, :48-60
+        mids = 0.5 * (t_lin[1:] + t_lin[:-1])
+        lower = torch.cat([t_lin[:1], mids]).unsqueeze(0).expand(n_rays, n_samples)
+        upper = torch.cat([mids, t_lin[-1:]]).unsqueeze(0).expand(n_rays, n_samples)
+        t = lower + (upper - lower) * jitter
+    return t
+
+
+def points_on_rays(rays_o, rays_d, t):
+    return rays_o.unsqueeze(1) + rays_d.unsqueeze(1) * t.unsqueeze(2)   # :63, :267
+
+
+# ----------------------------------------------------------------------------------------------
+# a-D  frequency encoding (src/models/encoding/freq.py:7-32, encoding/__init__.py:6-18)
+def freq_encode(x, n_freqs):
+    outs = [x]
+    for band in (2.0 ** torch.linspace(0.0, n_freqs - 1, steps=n_freqs)):
+        outs.append(torch.sin(x * band))
+        outs.append(torch.cos(x * band))
+    return torch.cat(outs, -1)
+
+
+# ----------------------------------------------------------------------------------------------
+# a-F  NeRF MLP (network.py:49-74) and a-E Network.forward (network.py:199-258)
+def nerf_mlp(sd, net, x, taps=None):
+    """x: [M, 90] = [PE(pts) 63 | PE(dir) 27] -> [M, 4] = (r, g, b, sigma) pre-activation."""
+    p = lambda name: (sd["%s.%s.weight" % (net, name)], sd["%s.%s.bias" % (net, name)])
+    pts, views = torch.split(x, [63, 27], dim=-1)
+    h = pts
+    for i in range(8):
+        h = F.relu(F.linear(h, *p("pts_linears.%d" % i)))
+        if taps is not None:
+            taps["h%d" % i] = h
+        if i == 4:
+            h = torch.cat([pts, h], -1)                     # skip: [pts63 | h256]
+    alpha = F.linear(h, *p("alpha_linear"))
+    feature = F.linear(h, *p("feature_linear"))
+    hv = torch.cat([feature, views], -1)                    # [feature256 | dir27]
+    hv = F.relu(F.linear(hv, *p("views_linears.0")))
+    rgb = F.linear(hv, *p("rgb_linear"))
+    return torch.cat([rgb, alpha], -1)
+
+
+def network_forward(sd, pts, viewdirs, valid_mask=None, model="", chunk=512):
+    """pts [R,S,3], viewdirs [R,3], valid_mask [R,S] bool|None -> raw [R,S,4]."""
+    net = "model_fine" if model == "fine" else "model"
+    R, S, _ = pts.shape
+    x = pts.reshape(-1, 3)
+    v = viewdirs[:, None].expand(R, S, 3).reshape(-1, 3)
+    if valid_mask is not None:
+        m = valid_mask.reshape(-1)
+        x, v = x[m], v[m]
+    emb = torch.cat([freq_encode(x, 10), freq_encode(v, 4)], -1).to(torch.float32)
+    outs = [nerf_mlp(sd, net, emb[i:i + chunk]) for i in range(0, emb.shape[0], chunk)]  # batchify
+    flat = torch.cat(outs, 0) if outs else emb.new_zeros((0, 4))
+    if valid_mask is None:
+        return flat.reshape(R, S, 4)
+    out = torch.zeros(R * S, 4)
+    out[m] = flat                                           # masked points -> raw = 0 (:235-253)
+    return out.reshape(R, S, 4)
+
+
+# ----------------------------------------------------------------------------------------------
+# a-G  weights (volume_renderer.py:67-96)
+def weights_computation(sigma, t):
+    delta = t[..., 1:] - t[..., :-1]
+    delta = torch.cat([delta, 1e10 * torch.ones_like(delta[..., :1])], -1)       # :80-81
+    alpha = 1.0 - torch.exp(-sigma * delta)                                      # :84
+    tmp = torch.cat([torch.ones(alpha.shape[0], 1), torch.clamp(1.0 - alpha, min=1e-10, max=1.0)], -1)
+    T = torch.cumprod(tmp, -1)[:, :-1]                                           # :87-91
+    return T, T * alpha                                                          # :94
+
+
+# a-H  hierarchical sampling (volume_renderer.py:98-272), default fast_sampling=False path
+def sample_pdf(sigma_c, t_c, n_importance, u=None, eps=1e-5, taps=None):
+    n_samples = t_c.shape[-1]
+    _, w = weights_computation(sigma_c, t_c)                    # :127
+    w = w[..., 1:-1] + eps                                      # :128, :137
+    pdf = w / torch.sum(w, -1, keepdim=True)
+    cdf = torch.cumsum(pdf, -1)
+    cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)  # [N, Nc-1]
+    if u is None:
+        u = torch.linspace(0.0, 1.0, steps=n_importance).expand(list(cdf.shape[:-1]) + [n_importance])
+    u = u.contiguous()
+    inds = torch.searchsorted(cdf, u, right=True)               # :151
+    below = torch.clamp(inds - 1, 0, n_samples - 3)             # :153  (the Nc-3 quirk, fact 7)
+    above = torch.clamp(inds, 0, n_samples - 3)                 # :154
+    bins = 0.5 * (t_c[..., 1:] + t_c[..., :-1])                 # :249
+    cdf0, cdf1 = torch.gather(cdf, 1, below), torch.gather(cdf, 1, above)
+    b0, b1 = torch.gather(bins, 1, below), torch.gather(bins, 1, above)
+    denom = cdf1 - cdf0
+    denom = torch.where(denom < eps, torch.ones_like(denom), denom)   # :259-260
+    tt = (u - cdf0) / denom
+    t_fine = b0 + tt * (b1 - b0)                                # :263-264
+    if taps is not None:
+        taps.update(cdf=cdf, inds=inds, below=below, above=above, bins=bins)
+    return t_fine
+
+
+# a-J composite (volume_renderer.py:414-430)
+def composite(raw, t, white_bkgd=True):
+    rgb = torch.sigmoid(raw[..., :3])
+    sigma = F.relu(raw[..., 3])
+    _, w = weights_computation(sigma, t)
+    rgb_map = torch.sum(w.unsqueeze(-1) * rgb, dim=1)
+    depth_map = torch.sum(w * t, dim=1)
+    acc = w.sum(-1)
+    if white_bkgd:
+        rgb_map = rgb_map + (1.0 - w.sum(dim=-1, keepdim=True))
+    return rgb_map, depth_map, acc, w
+
+
+# ----------------------------------------------------------------------------------------------
+# Renderer.render (volume_renderer.py:290-432)
+def render(sd, rays_o, rays_d, n_samples=64, n_importance=128, white_bkgd=True,
+           jitter=None, u=None, taps=None, chunk=512):
+    """rays_o/rays_d [N,3] fp32 -> (rgb [N,3], depth [N]) of the final pass.  ``taps`` (dict)
+    receives every intermediate; ``jitter``/``u`` inject the perturb / train-mode random numbers."""
+    N = rays_o.shape[0]
+    t_c = stratified_t(N, n_samples, jitter)
+    pts_c = points_on_rays(rays_o, rays_d, t_c)
+    viewdirs = rays_d / torch.norm(rays_d, dim=-1, keepdim=True)     # :314
+    raw_c = network_forward(sd, pts_c, viewdirs, None, "", chunk)
+    tp = {} if taps is None else taps
+    tp.update(t_coarse=t_c, raw_coarse=raw_c, viewdirs=viewdirs)
+    if n_importance > 0:
+        sigma_c = F.relu(raw_c[..., 3])                              # :335-338
+        t_f = sample_pdf(sigma_c, t_c, n_importance, u, taps=tp)
+        pts_f = points_on_rays(rays_o, rays_d, t_f)
+        depth = torch.cat([t_c, t_f], 1)
+        depth, idx = torch.sort(depth, dim=-1)                       # :353
+        pts = torch.gather(torch.cat([pts_c, pts_f], 1), 1, idx.unsqueeze(-1).expand(-1, -1, 3))
+        raw = torch.cat([network_forward(sd, pts[:, j:j + 64], viewdirs, None, "fine", chunk)
+                         for j in range(0, pts.shape[1], 64)], 1)    # :386-397 (sample blocks of 64)
+        tp.update(t_fine=t_f, depth_sorted=depth, sort_idx=idx, raw_fine=raw)
+        rgb_c, depth_c, acc_c, _ = composite(raw_c, t_c, white_bkgd)  # extension maps (fact 3)
+        tp.update(rgb_map_coarse=rgb_c, depth_map_coarse=depth_c, acc_map_coarse=acc_c)
+    else:
+        depth, raw = t_c, raw_c
+    rgb_map, depth_map, acc, w = composite(raw, depth, white_bkgd)
+    tp.update(weights=w, rgb_map=rgb_map, depth_map=depth_map, acc_map=acc)
+    return rgb_map, depth_map
+
+
+# ----------------------------------------------------------------------------------------------
+# a-K / a-L training step: trainers/nerf.py:27-33, trainer.py:56-60, train/optimizer.py:8-28
+class Trainer:
+    """render -> MSELoss -> backward -> clip_grad_value_(40) -> Adam(lr, eps=1e-8)."""
+
+    def __init__(self, sd, lr=5e-4, eps=1e-8, clip=40.0, **render_kw):
+        self.keys = state_dict_keys()
+        self.sd = {k: sd[k].detach().clone().requires_grad_(True) for k in self.keys}
+        groups = [{"params": [self.sd[k]], "lr": lr, "weight_decay": 0.0, "eps": eps} for k in self.keys]
+        self.opt = torch.optim.Adam(groups, lr, weight_decay=0.0, eps=eps)
+        self.clip = clip
+        self.render_kw = render_kw
+
+    def forward_backward(self, rays_o, rays_d, rgb_gt, world=1):
+        self.opt.zero_grad()
+        rgb, _ = render(self.sd, rays_o, rays_d, **self.render_kw)
+        loss = F.mse_loss(rgb, rgb_gt)
+        (loss / world).backward()
+        return loss.detach()
+
+    def grads_flat(self):
+        return torch.cat([(self.sd[k].grad if self.sd[k].grad is not None
+                           else torch.zeros_like(self.sd[k])).reshape(-1) for k in self.keys])
+
+    def set_grads_flat(self, flat):
+        o = 0
+        for k in self.keys:
+            n = self.sd[k].numel()
+            self.sd[k].grad = flat[o:o + n].reshape(self.sd[k].shape).clone()
+            o += n
+
+    def apply(self):
+        torch.nn.utils.clip_grad_value_(list(self.sd.values()), self.clip)
+        self.opt.step()
+
+    def step(self, rays_o, rays_d, rgb_gt):
+        loss = self.forward_backward(rays_o, rays_d, rgb_gt)
+        self.apply()
+        return float(loss)
+
+    def set_lr(self, lr):
+        for g in self.opt.param_groups:
+            g["lr"] = lr
+
+
+def synthetic_train_batch(step, rank, n_rays, H=800, W=800, n_views=8):
+    """SURVEY.md section 8d 'Training inputs'."""
+    g = torch.Generator().manual_seed(1000 * step + rank)
+    pix = torch.randint(0, H * W, (n_rays,), generator=g)
+    rgb_gt = torch.rand(n_rays, 3, generator=g)
+    c2w = lego_pose(step % n_views, n_views)
+    o, d = get_rays_np(c2w, H, W, pix.numpy())
+    return torch.from_numpy(o), torch.from_numpy(d), rgb_gt, pix, c2w
