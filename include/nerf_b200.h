@@ -1,0 +1,155 @@
+/*
+ * nerf_b200.h -- C ABI of libnerf_b200.so, the B200-native (sm_100a) NeRF ray-render / train engine.
+ *
+ * Drop-in boundary for rkin100g/Nerf-Replication's hot path.  The reference has no native ABI on this
+ * path (its only native code is the unused pybind hash encoder,
+ * src/models/encoding/hashencoder/src/bindings.cpp:5-8), so every entry point below cites the Python
+ * interface it replaces.  File:line citations are relative to the reference root.
+ *
+ * Conventions
+ *   - plain C: opaque handle, raw pointers, sizes; no torch / C++ types.
+ *   - every pointer is a DEVICE pointer on the handle's device unless the name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); every launch of a call
+ *     goes to that stream; calls are asynchronous unless documented otherwise (the *_host calls sync).
+ *   - the caller owns inputs/outputs; the engine owns its handle, workspace and packed weights.
+ *   - return value: 0 = NERF_OK, negative = NERF_E_*; nerf_last_error() has the message.  Unsupported
+ *     configurations are errors -- there is no CPU or library fallback anywhere.
+ *   - a handle is bound to one device, is not thread-safe, and is meant for one process per GPU.
+ *
+ * Flat parameter layout ("flat", NERF_PARAMS_TOTAL floats): the reference's Network.state_dict() order
+ * (network.py:22-47,144-161): for net in {model, model_fine}: pts_linears.0..7, views_linears.0,
+ * feature_linear, alpha_linear, rgb_linear; each as weight[out][in] (row-major, PyTorch layout) followed by
+ * bias[out].  Gradients, Adam moments use the same layout.
+ */
+#ifndef NERF_B200_H_
+#define NERF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NERF_OK 0
+#define NERF_E_INVALID (-1)     /* bad argument / unsupported configuration            */
+#define NERF_E_CUDA (-2)        /* a CUDA runtime call failed                          */
+#define NERF_E_NOMEM (-3)       /* workspace allocation failed                         */
+#define NERF_E_STATE (-4)       /* call order (e.g. render before nerf_set_params)     */
+
+#define NERF_PARAMS_PER_NET 595844
+#define NERF_PARAMS_TOTAL 1191688
+#define NERF_NUM_LAYERS 12      /* per net, in state_dict order                         */
+
+#define NERF_PRECISION_BF16 0   /* tcgen05 bf16 operands, fp32 accumulate (fast path)  */
+#define NERF_PRECISION_FP32 1   /* fp32 FFMA validation mode                           */
+
+#define NERF_NET_COARSE 0       /* Network.model       (network.py:144)                */
+#define NERF_NET_FINE 1         /* Network.model_fine  (network.py:154)                */
+
+typedef struct NerfEngine NerfEngine;
+
+/* Knobs of Renderer.__init__ (volume_renderer.py:9-24) + near/far (:27). */
+typedef struct NerfConfig {
+  int32_t n_samples;     /* cfg.N_samples      (64)                                   */
+  int32_t n_importance;  /* cfg.N_importance   (128); 0 = coarse only                 */
+  int32_t white_bkgd;    /* cfg.white_bkgd     (1)                                    */
+  int32_t perturb;       /* cfg.perturb && task=="train": jittered coarse t           */
+  int32_t train_u;       /* task=="train": u ~ U[0,1) instead of linspace (:143-147)  */
+  int32_t precision;     /* NERF_PRECISION_*                                          */
+  float t_near, t_far;   /* 2.0, 6.0                                                  */
+  uint64_t seed;         /* Philox seed for in-kernel jitter/u when no arrays given   */
+} NerfConfig;
+
+/* Optional outputs / taps of a render call; any pointer may be NULL. */
+typedef struct NerfRenderOut {
+  float* rgb;            /* [n,3]  final-pass rgb_map   (volume_renderer.py:425,432)  */
+  float* depth;          /* [n]    final-pass depth_map (:426)                        */
+  float* acc;            /* [n]    sum of weights (:430)                              */
+  float* rgb_coarse;     /* [n,3]  same maps for the coarse pass (extension)          */
+  float* depth_coarse;   /* [n]                                                       */
+  float* acc_coarse;     /* [n]                                                       */
+} NerfRenderOut;
+
+/* ---- lifecycle ------------------------------------------------------------------------------- */
+int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out);
+int nerf_destroy(NerfEngine* h);
+const char* nerf_last_error(const NerfEngine* h);        /* h may be NULL: last create() error   */
+int nerf_set_config(NerfEngine* h, const NerfConfig* cfg);
+/* Network parameters (replaces nn.Module ownership, network.py:126-161 / net_utils.py:346-379).
+ * `flat` stays owned by the caller and must stay alive: the engine reads fp32 masters from it and keeps a
+ * packed bf16 copy that nerf_set_params / nerf_clip_adam refresh. */
+int nerf_set_params(NerfEngine* h, const float* flat, void* stream);
+int nerf_version(void);
+/* Number of engine kernels launched through this handle since creation (bench.py's gpu_launches). */
+int64_t nerf_launch_count(const NerfEngine* h);
+
+/* ---- stage kernels (parity taps; each is also used by the fused calls) ------------------------- */
+/* a-B get_rays, src/datasets/nerf/blender.py:95-127.  c2w_host: 12 doubles (3x4 row-major).  pixel_ids
+ * (device int64[n]) or NULL for the pixel range [pix0, pix0+n) in row-major order. */
+int nerf_get_rays(NerfEngine* h, const double* c2w_host, int H, int W, double focal, double cx, double cy,
+                  const int64_t* pixel_ids, int64_t pix0, int64_t n, float* rays_o, float* rays_d, void* stream);
+/* a-C stratified t, volume_renderer.py:27-65.  jitter [n,S] or NULL (perturb=0 -> linspace). */
+int nerf_stratified_t(NerfEngine* h, int64_t n, int S, const float* jitter, float* t, void* stream);
+/* a-D Encoder.embed, src/models/encoding/freq.py:7-32.  x [m,3] -> out [m, 3+6*n_freqs] fp32. */
+int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, float* out, void* stream);
+/* a-E/a-F Network.forward, network.py:199-258.  pts [R,S,3], viewdirs [R,3], mask [R,S] uint8 or NULL,
+ * raw [R,S,4] = (r,g,b,sigma) pre-activation; masked-out points get raw = 0 (:235). */
+int nerf_mlp_forward(NerfEngine* h, int which_net, const float* pts, const float* viewdirs,
+                     const uint8_t* mask, int64_t R, int S, float* raw, void* stream);
+/* a-G + a-J weights_computation + composite, volume_renderer.py:67-96,414-430.
+ * raw [n,S,4], t [n,S] -> maps (any NULL skipped), weights [n,S] or NULL. */
+int nerf_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white_bkgd,
+                   float* rgb, float* depth, float* acc, float* weights, void* stream);
+/* a-H + a-I fine_sample_points + merge, volume_renderer.py:98-272,349-356.
+ * raw_c [n,Nc,4] (sigma = relu(raw[...,3])), t_c [n,Nc]; u [n,Nf] or NULL (linspace);
+ * cdf_in [n,Nc-1] or NULL (inject the oracle's cdf for bit-exact index parity).
+ * Outputs (any may be NULL): t_fine [n,Nf], inds/below/above int64 [n,Nf], cdf_out [n,Nc-1],
+ * t_sorted [n,Nc+Nf], sort_idx int32 [n,Nc+Nf] (index into cat[t_c,t_fine]). */
+int nerf_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
+                    const float* u, const float* cdf_in, float* t_fine, int64_t* inds, int64_t* below,
+                    int64_t* above, float* cdf_out, float* t_sorted, int32_t* sort_idx, void* stream);
+
+/* ---- the hot call: Renderer.render, volume_renderer.py:290-432 ------------------------------------ */
+int nerf_render_rays(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n,
+                     const float* jitter, const float* u, const NerfRenderOut* out, void* stream);
+/* camera mode: get_rays fused in front (pixels [pix0, pix0+n) of an HxW view). */
+int nerf_render_camera(NerfEngine* h, const double* c2w_host, int H, int W, double focal, double cx,
+                       double cy, int64_t pix0, int64_t n, const NerfRenderOut* out, void* stream);
+/* Host-buffer variant (the e2e path): pageable or pinned host arrays in, host maps out; H2D/D2H are
+ * chunked and overlapped with compute on internal streams; synchronous on return. */
+int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, const float* rays_d_host, int64_t n,
+                          float* rgb_host, float* depth_host);
+
+/* ---- training: trainers/nerf.py:27-33 (MSE), trainer.py:56-60, train/optimizer.py:8-28 ------------- */
+/* loss = mean((render(rays)-rgb_gt)^2); writes d loss/d params * grad_scale into flat_grad (overwritten,
+ * not accumulated), loss into *loss (device float).  Follows the reference autograd graph incl. the
+ * un-detached t_fine path. */
+int nerf_forward_backward(NerfEngine* h, const float* rays_o, const float* rays_d, const float* rgb_gt,
+                          int64_t n, const float* jitter, const float* u, float grad_scale,
+                          float* loss, float* flat_grad, float* rgb_out, void* stream);
+/* Split form used by the autograd drop-in (Renderer.render under torch.enable_grad()): the forward keeps
+ * its activations inside the handle until the matching backward.  d_rgb [n,3] / d_depth [n] are the incoming
+ * gradients of the maps (either may be NULL); gradients are accumulated into flat_grad (zeroed first when
+ * zero_grad != 0). */
+int nerf_train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
+                       const float* u, float* rgb, float* depth, void* stream);
+int nerf_train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
+                        const float* d_depth, float* flat_grad, int zero_grad, void* stream);
+/* g = clamp(g,-clip,clip) (clip<=0: off); torch.optim.Adam step `step` (1-based), weight_decay 0;
+ * updates flat_param/m/v in place and refreshes the engine's packed bf16 weights. */
+int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* flat_grad, float* m, float* v,
+                   float lr, float beta1, float beta2, float eps, float clip, int step, void* stream);
+
+/* ---- debug / bring-up ------------------------------------------------------------------------------ */
+/* tcgen05 descriptor probe battery (see csrc/probe.cu); writes results for `variant` into out[]. */
+int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K,
+                          void* stream);
+
+/* watchdog record of the tcgen05 kernels: a barrier that never completes traps the kernel instead of
+ * hanging the GPU and leaves {tag, blockIdx, threadIdx, parity, ...} here.  out8: 8 uint32 (host). */
+int nerf_debug_tc_watchdog(unsigned int* out8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H_ */

@@ -1,0 +1,430 @@
+// api.cu -- the extern "C" boundary (include/nerf_b200.h) and the render / train-step orchestration.
+// Renderer.render (volume_renderer.py:290-432) becomes: stratified t -> coarse MLP -> sample_pdf+merge ->
+// fine MLP -> composite, each a kernel of this library launched on the caller's stream.
+#include <algorithm>
+#include <cstring>
+#include "engine.h"
+
+namespace nerf {
+int tc_debug_read(unsigned int out[8]);
+}
+using namespace nerf;
+
+static std::string g_create_error;
+
+static int check_cfg(const NerfConfig& c, std::string* why) {
+  if (c.n_samples < 4 || c.n_samples > 1024) { *why = "n_samples must be in [4,1024]"; return NERF_E_INVALID; }
+  if (c.n_importance < 0 || c.n_samples + c.n_importance > 4096) { *why = "n_importance out of range"; return NERF_E_INVALID; }
+  if (c.precision != NERF_PRECISION_BF16 && c.precision != NERF_PRECISION_FP32) { *why = "unknown precision"; return NERF_E_INVALID; }
+  if (!(c.t_far > c.t_near)) { *why = "t_far must exceed t_near"; return NERF_E_INVALID; }
+  return NERF_OK;
+}
+
+extern "C" int nerf_version(void) { return 100; }
+
+extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) {
+  if (!cfg || !out) { g_create_error = "null argument"; return NERF_E_INVALID; }
+  std::string why;
+  if (check_cfg(*cfg, &why)) { g_create_error = why; return NERF_E_INVALID; }
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || device < 0 || device >= count) {
+    g_create_error = std::string("no such CUDA device (") + (e == cudaSuccess ? "index out of range" : cudaGetErrorString(e)) + "); the engine has no CPU fallback";
+    cudaGetLastError();
+    return NERF_E_CUDA;
+  }
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  if (prop.major != 10) {
+    g_create_error = "device is sm_" + std::to_string(prop.major * 10 + prop.minor) + "; this library is built for sm_100a (B200) only";
+    return NERF_E_INVALID;
+  }
+  cudaSetDevice(device);
+  NerfEngine* h = new NerfEngine();
+  h->cfg = *cfg;
+  h->device = device;
+  h->num_sms = prop.multiProcessorCount;
+  *out = h;
+  return NERF_OK;
+}
+
+extern "C" int nerf_destroy(NerfEngine* h) {
+  if (!h) return NERF_OK;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
+  if (h->wpack) cudaFree(h->wpack);
+  for (int i = 0; i < 2; ++i) {
+    if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
+    if (h->hev[i]) cudaEventDestroy(h->hev[i]);
+    if (h->pinned[i]) cudaFreeHost(h->pinned[i]);
+  }
+  cudaGetLastError();
+  delete h;
+  return NERF_OK;
+}
+
+extern "C" const char* nerf_last_error(const NerfEngine* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+extern "C" int64_t nerf_launch_count(const NerfEngine* h) { return h ? h->launches : 0; }
+
+extern "C" int nerf_set_config(NerfEngine* h, const NerfConfig* cfg) {
+  if (!h || !cfg) return NERF_E_INVALID;
+  std::string why;
+  if (check_cfg(*cfg, &why)) return h->fail(NERF_E_INVALID, why);
+  h->cfg = *cfg;
+  return NERF_OK;
+}
+
+static int post(NerfEngine* h, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  return NERF_OK;
+}
+
+extern "C" int nerf_set_params(NerfEngine* h, const float* flat, void* stream) {
+  if (!h || !flat) return NERF_E_INVALID;
+  if (reinterpret_cast<uintptr_t>(flat) & 15) return h->fail(NERF_E_INVALID, "flat parameter buffer must be 16-byte aligned");
+  cudaSetDevice(h->device);
+  h->params = flat;
+  if (!h->wpack) {
+    h->wpack_bytes = tc_wpack_bytes();
+    NERF_CUDA_TRY(h, cudaMalloc(&h->wpack, h->wpack_bytes));
+    NERF_CUDA_TRY(h, cudaMemsetAsync(h->wpack, 0, h->wpack_bytes, (cudaStream_t)stream));
+  }
+  tc_pack_weights(h, flat, h->wpack, (cudaStream_t)stream);
+  h->params_set = true;
+  return post(h, "nerf_set_params");
+}
+
+// ---- stage entry points ---------------------------------------------------------------------------
+static Camera make_camera(const double* c2w, int H, int W, double focal, double cx, double cy) {
+  Camera cam{};
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) { cam.r64[3 * r + c] = c2w[4 * r + c]; cam.r[3 * r + c] = (float)c2w[4 * r + c]; }
+    cam.o64[r] = c2w[4 * r + 3]; cam.o[r] = (float)c2w[4 * r + 3];
+  }
+  cam.focal = focal; cam.cx = cx; cam.cy = cy; cam.H = H; cam.W = W;
+  return cam;
+}
+
+extern "C" int nerf_get_rays(NerfEngine* h, const double* c2w_host, int H, int W, double focal, double cx, double cy,
+                             const int64_t* pixel_ids, int64_t pix0, int64_t n, float* rays_o, float* rays_d, void* stream) {
+  if (!h || !c2w_host || !rays_o || !rays_d || n < 0 || H <= 0 || W <= 0) return h ? h->fail(NERF_E_INVALID, "nerf_get_rays: bad argument") : NERF_E_INVALID;
+  if (!pixel_ids && (pix0 < 0 || pix0 + n > (int64_t)H * W)) return h->fail(NERF_E_INVALID, "nerf_get_rays: pixel range outside the image");
+  cudaSetDevice(h->device);
+  launch_get_rays(h, make_camera(c2w_host, H, W, focal, cx, cy), pixel_ids, pix0, n, rays_o, rays_d, (cudaStream_t)stream);
+  return post(h, "nerf_get_rays");
+}
+
+extern "C" int nerf_stratified_t(NerfEngine* h, int64_t n, int S, const float* jitter, float* t, void* stream) {
+  if (!h || !t || n < 0 || S < 2) return h ? h->fail(NERF_E_INVALID, "nerf_stratified_t: bad argument") : NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  launch_stratified_t(h, n, S, jitter, false, 0, t, (cudaStream_t)stream);
+  return post(h, "nerf_stratified_t");
+}
+
+extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, float* out, void* stream) {
+  if (!h || !x || !out || m < 0 || n_freqs < 0 || n_freqs > 16) return h ? h->fail(NERF_E_INVALID, "nerf_freq_encode: bad argument") : NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  launch_freq_encode(h, x, m, n_freqs, out, (cudaStream_t)stream);
+  return post(h, "nerf_freq_encode");
+}
+
+static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep, cudaStream_t st) {
+  if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_forward(h, net, src, raw, keep, st);
+  return mlp_tc_forward(h, net, src, raw, st);
+}
+
+extern "C" int nerf_mlp_forward(NerfEngine* h, int which_net, const float* pts, const float* viewdirs, const uint8_t* mask,
+                                int64_t R, int S, float* raw, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_mlp_forward before nerf_set_params");
+  if (!pts || !viewdirs || !raw || R < 0 || S < 1 || (which_net != NERF_NET_COARSE && which_net != NERF_NET_FINE))
+    return h->fail(NERF_E_INVALID, "nerf_mlp_forward: bad argument");
+  cudaSetDevice(h->device);
+  RowSrc src;
+  src.pts = pts; src.viewdirs = viewdirs; src.mask = mask; src.R = R; src.S = S;
+  int rc = run_mlp(h, which_net, src, raw, false, (cudaStream_t)stream);
+  return rc ? rc : post(h, "nerf_mlp_forward");
+}
+
+extern "C" int nerf_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white_bkgd, float* rgb,
+                              float* depth, float* acc, float* weights, void* stream) {
+  if (!h || !raw || !t || n < 0 || S < 1) return h ? h->fail(NERF_E_INVALID, "nerf_composite: bad argument") : NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  launch_composite(h, raw, t, n, S, white_bkgd, rgb, depth, acc, weights, (cudaStream_t)stream);
+  return post(h, "nerf_composite");
+}
+
+extern "C" int nerf_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf, const float* u,
+                               const float* cdf_in, float* t_fine, int64_t* inds, int64_t* below, int64_t* above,
+                               float* cdf_out, float* t_sorted, int32_t* sort_idx, void* stream) {
+  if (!h || !raw_c || !t_c || n < 0) return h ? h->fail(NERF_E_INVALID, "nerf_sample_pdf: bad argument") : NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  int rc = launch_sample_pdf(h, raw_c, t_c, n, Nc, Nf, u, false, 0, cdf_in, t_fine, inds, below, above, cdf_out, t_sorted,
+                             sort_idx, (cudaStream_t)stream);
+  return rc ? rc : post(h, "nerf_sample_pdf");
+}
+
+// ---- Renderer.render ----------------------------------------------------------------------------
+struct RenderTaps {   // device workspace of one chunk; kept for the backward pass
+  float *t_c = nullptr, *raw_c = nullptr, *t_s = nullptr, *raw_f = nullptr;
+  int32_t* sort_idx = nullptr;
+  uint64_t call_id = 0;
+};
+
+static uint64_t g_call_counter = 0;
+
+// One chunk of rays through the whole pipeline.  `slot` selects a private workspace (host path ping-pong).
+static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n, const float* jitter, const float* u,
+                        const NerfRenderOut& out, bool keep, int slot, RenderTaps* taps, cudaStream_t st) {
+  const NerfConfig& c = h->cfg;
+  const int Nc = c.n_samples, Nf = c.n_importance, Nt = Nc + Nf;
+  const uint64_t call_id = ++g_call_counter;
+  char nm[4][32];
+  snprintf(nm[0], 32, "r%d.t_c", slot); snprintf(nm[1], 32, "r%d.raw_c", slot);
+  snprintf(nm[2], 32, "r%d.t_s", slot); snprintf(nm[3], 32, "r%d.raw_f", slot);
+  RenderTaps tp;
+  tp.call_id = call_id;
+  int rc;
+  if ((rc = h->buf(nm[0], (size_t)n * Nc, &tp.t_c))) return rc;
+  if ((rc = h->buf(nm[1], (size_t)n * Nc * 4, &tp.raw_c))) return rc;
+  const bool perturb = c.perturb != 0;
+  launch_stratified_t(h, n, Nc, perturb ? jitter : nullptr, perturb && !jitter, call_id, tp.t_c, st);
+  RowSrc src;
+  src.rays_o = o; src.rays_d = d; src.t = tp.t_c; src.R = n; src.S = Nc;
+  if ((rc = run_mlp(h, NERF_NET_COARSE, src, tp.raw_c, keep, st))) return rc;
+  if (Nf > 0) {
+    if ((rc = h->buf(nm[2], (size_t)n * Nt, &tp.t_s))) return rc;
+    if ((rc = h->buf(nm[3], (size_t)n * Nt * 4, &tp.raw_f))) return rc;
+    if (keep) {
+      char nb[32]; snprintf(nb, 32, "r%d.sort_idx", slot);
+      if ((rc = h->buf(nb, (size_t)n * Nt, &tp.sort_idx))) return rc;
+    }
+    const bool tu = c.train_u != 0;
+    if ((rc = launch_sample_pdf(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? u : nullptr, tu && !u, call_id, nullptr, nullptr, nullptr,
+                                nullptr, nullptr, nullptr, tp.t_s, tp.sort_idx, st))) return rc;
+    src.t = tp.t_s; src.S = Nt;
+    if ((rc = run_mlp(h, NERF_NET_FINE, src, tp.raw_f, keep, st))) return rc;
+    launch_composite(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
+    if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)
+      launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb_coarse, out.depth_coarse, out.acc_coarse, nullptr, st);
+  } else {
+    launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
+    if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)
+      launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb_coarse, out.depth_coarse, out.acc_coarse, nullptr, st);
+  }
+  if (taps) *taps = tp;
+  return post(h, "render");
+}
+
+static NerfRenderOut offset_out(const NerfRenderOut& o, int64_t r) {
+  NerfRenderOut q = o;
+  if (q.rgb) q.rgb += 3 * r;
+  if (q.depth) q.depth += r;
+  if (q.acc) q.acc += r;
+  if (q.rgb_coarse) q.rgb_coarse += 3 * r;
+  if (q.depth_coarse) q.depth_coarse += r;
+  if (q.acc_coarse) q.acc_coarse += r;
+  return q;
+}
+
+constexpr int64_t kRenderChunk = 65536;   // rays per pass: bounds the HBM workspace (~5 KB/ray at 64+128)
+
+extern "C" int nerf_render_rays(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
+                                const float* u, const NerfRenderOut* out, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_rays before nerf_set_params");
+  if (!rays_o || !rays_d || !out || n < 0) return h->fail(NERF_E_INVALID, "nerf_render_rays: bad argument");
+  cudaSetDevice(h->device);
+  const int Nc = h->cfg.n_samples, Nf = h->cfg.n_importance;
+  for (int64_t r = 0; r < n; r += kRenderChunk) {
+    const int64_t m = std::min(kRenderChunk, n - r);
+    int rc = render_chunk(h, rays_o + 3 * r, rays_d + 3 * r, m, jitter ? jitter + r * Nc : nullptr, u ? u + r * Nf : nullptr,
+                          offset_out(*out, r), false, 0, nullptr, (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return NERF_OK;
+}
+
+extern "C" int nerf_render_camera(NerfEngine* h, const double* c2w_host, int H, int W, double focal, double cx, double cy,
+                                  int64_t pix0, int64_t n, const NerfRenderOut* out, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_camera before nerf_set_params");
+  if (!c2w_host || !out || n < 0 || pix0 < 0 || pix0 + n > (int64_t)H * W) return h->fail(NERF_E_INVALID, "nerf_render_camera: bad argument");
+  cudaSetDevice(h->device);
+  const Camera cam = make_camera(c2w_host, H, W, focal, cx, cy);
+  for (int64_t r = 0; r < n; r += kRenderChunk) {
+    const int64_t m = std::min(kRenderChunk, n - r);
+    float *o, *d;
+    int rc;
+    if ((rc = h->buf("cam.o", (size_t)m * 3, &o))) return rc;
+    if ((rc = h->buf("cam.d", (size_t)m * 3, &d))) return rc;
+    launch_get_rays(h, cam, nullptr, pix0 + r, m, o, d, (cudaStream_t)stream);
+    if ((rc = render_chunk(h, o, d, m, nullptr, nullptr, offset_out(*out, r), false, 0, nullptr, (cudaStream_t)stream))) return rc;
+  }
+  return NERF_OK;
+}
+
+// Host-buffer path: chunks ping-pong over two internal streams so the H2D of chunk i+1 and the D2H of
+// chunk i-1 overlap the kernels of chunk i.  (fp32 validation mode shares one MLP workspace -> one stream.)
+extern "C" int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, const float* rays_d_host, int64_t n,
+                                     float* rgb_host, float* depth_host) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_rays_host before nerf_set_params");
+  if (!rays_o_host || !rays_d_host || !rgb_host || !depth_host || n < 0) return h->fail(NERF_E_INVALID, "nerf_render_rays_host: bad argument");
+  cudaSetDevice(h->device);
+  const int nslots = h->cfg.precision == NERF_PRECISION_FP32 ? 1 : 2;
+  const size_t per_ray = 10 * sizeof(float);   // o3 d3 rgb3 depth1
+  const size_t need = (size_t)kRenderChunk * per_ray;
+  for (int i = 0; i < 2; ++i) {
+    if (!h->hs[i]) NERF_CUDA_TRY(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
+    if (!h->hev[i]) NERF_CUDA_TRY(h, cudaEventCreateWithFlags(&h->hev[i], cudaEventDisableTiming));
+    if (h->pinned_bytes < need) {
+      if (h->pinned[i]) cudaFreeHost(h->pinned[i]);
+      NERF_CUDA_TRY(h, cudaMallocHost(&h->pinned[i], need));
+    }
+  }
+  h->pinned_bytes = std::max(h->pinned_bytes, need);
+  struct Pending { int64_t r = -1, m = 0; } pend[2];
+  auto drain = [&](int s) {   // wait for slot s and copy its maps out of pinned memory
+    if (pend[s].r < 0) return;
+    cudaEventSynchronize(h->hev[s]);
+    const float* pin = reinterpret_cast<const float*>(h->pinned[s]);
+    memcpy(rgb_host + 3 * pend[s].r, pin + 6 * kRenderChunk, (size_t)pend[s].m * 3 * sizeof(float));
+    memcpy(depth_host + pend[s].r, pin + 9 * kRenderChunk, (size_t)pend[s].m * sizeof(float));
+    pend[s].r = -1;
+  };
+  int64_t ci = 0;
+  for (int64_t r = 0; r < n; r += kRenderChunk, ++ci) {
+    const int s = (int)(ci % nslots);
+    drain(s);
+    const int64_t m = std::min(kRenderChunk, n - r);
+    float* pin = reinterpret_cast<float*>(h->pinned[s]);
+    memcpy(pin, rays_o_host + 3 * r, (size_t)m * 3 * sizeof(float));
+    memcpy(pin + 3 * kRenderChunk, rays_d_host + 3 * r, (size_t)m * 3 * sizeof(float));
+    float *o, *d, *rgb, *dep;
+    char nm[32];
+    int rc;
+    snprintf(nm, 32, "h%d.o", s); if ((rc = h->buf(nm, (size_t)kRenderChunk * 3, &o))) return rc;
+    snprintf(nm, 32, "h%d.d", s); if ((rc = h->buf(nm, (size_t)kRenderChunk * 3, &d))) return rc;
+    snprintf(nm, 32, "h%d.rgb", s); if ((rc = h->buf(nm, (size_t)kRenderChunk * 3, &rgb))) return rc;
+    snprintf(nm, 32, "h%d.dep", s); if ((rc = h->buf(nm, (size_t)kRenderChunk, &dep))) return rc;
+    cudaStream_t st = h->hs[s];
+    NERF_CUDA_TRY(h, cudaMemcpyAsync(o, pin, (size_t)m * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    NERF_CUDA_TRY(h, cudaMemcpyAsync(d, pin + 3 * kRenderChunk, (size_t)m * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    NerfRenderOut out{};
+    out.rgb = rgb; out.depth = dep;
+    if ((rc = render_chunk(h, o, d, m, nullptr, nullptr, out, false, 1 + s, nullptr, st))) return rc;
+    NERF_CUDA_TRY(h, cudaMemcpyAsync(pin + 6 * kRenderChunk, rgb, (size_t)m * 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    NERF_CUDA_TRY(h, cudaMemcpyAsync(pin + 9 * kRenderChunk, dep, (size_t)m * sizeof(float), cudaMemcpyDeviceToHost, st));
+    NERF_CUDA_TRY(h, cudaEventRecord(h->hev[s], st));
+    pend[s].r = r; pend[s].m = m;
+  }
+  for (int s = 0; s < 2; ++s) drain(s);
+  return post(h, "nerf_render_rays_host");
+}
+
+// ---- training step ------------------------------------------------------------------------------
+// loss = MSE(render(rays), rgb_gt) (trainers/nerf.py:27-33); backward follows the reference autograd
+// graph: fine MLP gets rgb+sigma gradients and an input gradient that flows
+// through PE -> t_fine -> inverse CDF -> coarse weights -> coarse sigma -> coarse trunk.
+static int train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
+                         const float* u, float* rgb, float* depth, cudaStream_t st) {
+  if (h->cfg.precision != NERF_PRECISION_FP32)
+    return h->fail(NERF_E_INVALID, "training: the backward pass exists in NERF_PRECISION_FP32 mode only in this build");
+  NerfRenderOut out{};
+  out.rgb = rgb; out.depth = depth;
+  RenderTaps tp;
+  int rc = render_chunk(h, rays_o, rays_d, n, jitter, u, out, true, 9, &tp, st);
+  if (rc) { h->taps.n = -1; return rc; }
+  h->taps.t_c = tp.t_c; h->taps.raw_c = tp.raw_c; h->taps.t_s = tp.t_s; h->taps.raw_f = tp.raw_f;
+  h->taps.sort_idx = tp.sort_idx; h->taps.call_id = tp.call_id; h->taps.n = n; h->taps.jitter = jitter; h->taps.u = u;
+  return NERF_OK;
+}
+
+static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
+                          const float* d_depth, float* flat_grad, cudaStream_t st) {
+  if (h->taps.n != n) return h->fail(NERF_E_STATE, "train_backward: no matching nerf_train_forward");
+  const NerfConfig& c = h->cfg;
+  const int Nc = c.n_samples, Nf = c.n_importance, Nt = Nc + Nf;
+  const NerfEngine::Taps& tp = h->taps;
+  int rc;
+  RowSrc src;
+  src.rays_o = rays_o; src.rays_d = rays_d; src.R = n;
+  if (Nf > 0) {
+    float *d_raw_f, *d_t_s, *d_w_c, *d_raw_c;
+    if ((rc = h->buf("tr.d_raw_f", (size_t)n * Nt * 4, &d_raw_f))) return rc;
+    if ((rc = h->buf("tr.d_t_s", (size_t)n * Nt, &d_t_s))) return rc;
+    if ((rc = h->buf("tr.d_w_c", (size_t)n * Nc, &d_w_c))) return rc;
+    if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
+    launch_composite_bwd(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_f, d_t_s, st);
+    src.t = tp.t_s; src.S = Nt;
+    if ((rc = mlp_fp32_backward(h, NERF_NET_FINE, src, d_raw_f, false, flat_grad + NERF_PARAMS_PER_NET, d_t_s, st))) return rc;
+    const bool tu = c.train_u != 0;
+    if ((rc = launch_sample_pdf_bwd(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? tp.u : nullptr, tu && !tp.u, tp.call_id, d_t_s,
+                                    tp.sort_idx, d_w_c, st))) return rc;
+    launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, nullptr, nullptr, d_w_c, d_raw_c, nullptr, st);
+    src.t = tp.t_c; src.S = Nc;
+    if ((rc = mlp_fp32_backward(h, NERF_NET_COARSE, src, d_raw_c, true, flat_grad, nullptr, st))) return rc;
+  } else {
+    float* d_raw_c;
+    if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
+    launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_c, nullptr, st);
+    src.t = tp.t_c; src.S = Nc;
+    if ((rc = mlp_fp32_backward(h, NERF_NET_COARSE, src, d_raw_c, false, flat_grad, nullptr, st))) return rc;
+  }
+  return post(h, "train_backward");
+}
+
+extern "C" int nerf_train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
+                                  const float* u, float* rgb, float* depth, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_train_forward before nerf_set_params");
+  if (!rays_o || !rays_d || !rgb || n <= 0) return h->fail(NERF_E_INVALID, "nerf_train_forward: bad argument");
+  cudaSetDevice(h->device);
+  return train_forward(h, rays_o, rays_d, n, jitter, u, rgb, depth, (cudaStream_t)stream);
+}
+
+extern "C" int nerf_train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
+                                   const float* d_depth, float* flat_grad, int zero_grad, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!rays_o || !rays_d || !flat_grad || n <= 0 || (!d_rgb && !d_depth)) return h->fail(NERF_E_INVALID, "nerf_train_backward: bad argument");
+  cudaSetDevice(h->device);
+  if (zero_grad) NERF_CUDA_TRY(h, cudaMemsetAsync(flat_grad, 0, (size_t)NERF_PARAMS_TOTAL * sizeof(float), (cudaStream_t)stream));
+  return train_backward(h, rays_o, rays_d, n, d_rgb, d_depth, flat_grad, (cudaStream_t)stream);
+}
+
+extern "C" int nerf_forward_backward(NerfEngine* h, const float* rays_o, const float* rays_d, const float* rgb_gt, int64_t n,
+                                     const float* jitter, const float* u, float grad_scale, float* loss, float* flat_grad,
+                                     float* rgb_out, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_forward_backward before nerf_set_params");
+  if (!rays_o || !rays_d || !rgb_gt || !loss || !flat_grad || n <= 0) return h->fail(NERF_E_INVALID, "nerf_forward_backward: bad argument");
+  cudaSetDevice(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  float *rgb, *d_rgb;
+  if ((rc = h->buf("tr.rgb", (size_t)n * 3, &rgb))) return rc;
+  if ((rc = h->buf("tr.d_rgb", (size_t)n * 3, &d_rgb))) return rc;
+  NERF_CUDA_TRY(h, cudaMemsetAsync(flat_grad, 0, (size_t)NERF_PARAMS_TOTAL * sizeof(float), st));
+  if ((rc = train_forward(h, rays_o, rays_d, n, jitter, u, rgb, nullptr, st))) return rc;
+  launch_mse_grad(h, rgb, rgb_gt, n, grad_scale, d_rgb, loss, st);
+  if (rgb_out) NERF_CUDA_TRY(h, cudaMemcpyAsync(rgb_out, rgb, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  return train_backward(h, rays_o, rays_d, n, d_rgb, nullptr, flat_grad, st);
+}
+
+extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* flat_grad, float* m, float* v, float lr, float beta1,
+                              float beta2, float eps, float clip, int step, void* stream) {
+  if (!h || !flat_param || !flat_grad || !m || !v || step < 1) return h ? h->fail(NERF_E_INVALID, "nerf_clip_adam: bad argument") : NERF_E_INVALID;
+  if ((reinterpret_cast<uintptr_t>(flat_param) | reinterpret_cast<uintptr_t>(flat_grad) | reinterpret_cast<uintptr_t>(m) |
+       reinterpret_cast<uintptr_t>(v)) & 15)
+    return h->fail(NERF_E_INVALID, "nerf_clip_adam: buffers must be 16-byte aligned");
+  cudaSetDevice(h->device);
+  launch_clip_adam(h, flat_param, flat_grad, m, v, NERF_PARAMS_TOTAL, lr, beta1, beta2, eps, clip, step, (cudaStream_t)stream);
+  if (h->params_set && flat_param == h->params && h->wpack) tc_pack_weights(h, flat_param, h->wpack, (cudaStream_t)stream);
+  return post(h, "nerf_clip_adam");
+}
+
+// watchdog record of the tcgen05 kernels (valid after a trapped launch); out: 8 uint32
+extern "C" int nerf_debug_tc_watchdog(unsigned int* out8) { return nerf::tc_debug_read(out8); }

@@ -1,0 +1,116 @@
+// engine.h -- the opaque handle behind the C ABI and the launchers each .cu file provides.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+#include "common.cuh"
+
+struct NerfEngine {
+  NerfConfig cfg{};
+  int device = 0;
+  int num_sms = 148;
+  std::string err;
+  int64_t launches = 0;
+
+  const float* params = nullptr;   // caller-owned fp32 masters (flat layout)
+  __nv_bfloat16* wpack = nullptr;  // packed bf16 weight images for the tcgen05 kernels
+  size_t wpack_bytes = 0;
+  bool params_set = false;
+
+  // grow-only named workspace buffers
+  struct Buf { void* p = nullptr; size_t bytes = 0; };
+  std::map<std::string, Buf> ws;
+
+  // taps of the last training forward (nerf_train_forward), consumed by nerf_train_backward
+  struct Taps { float *t_c = nullptr, *raw_c = nullptr, *t_s = nullptr, *raw_f = nullptr; int32_t* sort_idx = nullptr;
+                uint64_t call_id = 0; int64_t n = -1; const float *jitter = nullptr, *u = nullptr; } taps;
+
+  // host-path resources (nerf_render_rays_host)
+  cudaStream_t hs[2] = {nullptr, nullptr};
+  cudaEvent_t hev[2] = {nullptr, nullptr};
+  void* pinned[2] = {nullptr, nullptr};
+  size_t pinned_bytes = 0;
+
+  int fail(int code, const std::string& m) { err = m; return code; }
+
+  template <typename T>
+  int buf(const char* name, size_t count, T** out) {
+    Buf& b = ws[name];
+    size_t need = count * sizeof(T);
+    if (need == 0) need = sizeof(T);
+    if (b.bytes < need) {
+      if (b.p) {
+        // other streams may still use the old block: full sync before freeing (rare, grow-only)
+        cudaDeviceSynchronize();
+        cudaFree(b.p);
+        b.p = nullptr; b.bytes = 0;
+      }
+      size_t grow = need + need / 8;
+      cudaError_t e = cudaMalloc(&b.p, grow);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(NERF_E_NOMEM, std::string("cudaMalloc(") + name + ", " + std::to_string(grow) + " B): " + cudaGetErrorString(e));
+      }
+      b.bytes = grow;
+    }
+    *out = reinterpret_cast<T*>(b.p);
+    return NERF_OK;
+  }
+};
+
+namespace nerf {
+
+// ---- stages.cu ---------------------------------------------------------------------------------
+struct Camera { float r[9]; float o[3]; double r64[9]; double o64[3]; double focal, cx, cy; int H, W; };
+void launch_get_rays(NerfEngine* h, const Camera& cam, const int64_t* pixel_ids, int64_t pix0, int64_t n,
+                     float* rays_o, float* rays_d, cudaStream_t st);
+void launch_stratified_t(NerfEngine* h, int64_t n, int S, const float* jitter, bool philox, uint64_t call_id,
+                         float* t, cudaStream_t st);
+void launch_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, float* out, cudaStream_t st);
+void launch_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white,
+                      float* rgb, float* depth, float* acc, float* weights, cudaStream_t st);
+int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
+                      const float* u, bool philox_u, uint64_t call_id, const float* cdf_in, float* t_fine,
+                      int64_t* inds, int64_t* below, int64_t* above, float* cdf_out, float* t_sorted,
+                      int32_t* sort_idx, cudaStream_t st);
+// backward stages
+void launch_mse_grad(NerfEngine* h, const float* rgb, const float* gt, int64_t n, float scale,
+                     float* d_rgb, float* loss, cudaStream_t st);
+// composite backward: d_rgb_map [n,3] / d_depth_map [n] (or NULL) and/or direct d_w [n,S] (or NULL) -> d_raw [n,S,4] (rgb
+// channels zero when d_rgb_map NULL), d_t [n,S] (or NULL; gradient w.r.t. the sample depths).
+void launch_composite_bwd(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white,
+                          const float* d_rgb_map, const float* d_depth_map, const float* d_w, float* d_raw, float* d_t,
+                          cudaStream_t st);
+// sample_pdf backward: d_t_sorted [n,Nt] (total gradient at sorted positions) -> d_w_coarse [n,Nc]
+int launch_sample_pdf_bwd(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
+                          const float* u, bool philox_u, uint64_t call_id, const float* d_t_sorted,
+                          const int32_t* sort_idx, float* d_w_coarse, cudaStream_t st);
+
+// ---- mlp_fp32.cu -------------------------------------------------------------------------------
+// Row source for the MLP kernels: either explicit points or rays + depths.
+struct RowSrc {
+  const float* pts = nullptr;       // [R*S,3] explicit points (mode B) or NULL
+  const float* viewdirs = nullptr;  // [R,3] unit view dirs (mode B) or NULL -> normalise rays_d
+  const float* rays_o = nullptr;    // [R,3]
+  const float* rays_d = nullptr;    // [R,3]
+  const float* t = nullptr;         // [R,S]
+  const uint8_t* mask = nullptr;    // [R,S] or NULL
+  int64_t R = 0;
+  int S = 0;
+};
+int mlp_fp32_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep_acts, cudaStream_t st);
+// backward of the last keep_acts forward of `net`: d_raw [M,4] -> flat_grad (+=), d_t [R,S] (+=, may be NULL)
+int mlp_fp32_backward(NerfEngine* h, int net, const RowSrc& src, const float* d_raw, bool coarse_only_sigma,
+                      float* flat_grad_net, float* d_t, cudaStream_t st);
+
+// ---- mlp_tc.cu (tcgen05) ------------------------------------------------------------------------
+size_t tc_wpack_bytes();
+void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
+int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
+
+// ---- adam.cu -----------------------------------------------------------------------------------
+void launch_clip_adam(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr,
+                      float b1, float b2, float eps, float clip, int step, cudaStream_t st);
+void launch_fill(NerfEngine* h, float* p, int64_t n, float v, cudaStream_t st);
+
+}  // namespace nerf

@@ -1,0 +1,108 @@
+// probe.cu -- bring-up battery for the hand-written tcgen05 path: one CTA, one 128 x N x K bf16 GEMM,
+// operands staged through shared memory (or TMEM for A) in each layout the engine uses.  Lets a GPU run
+// tell descriptor/layout bugs apart from pipeline bugs in the fused kernels.
+//   variant 0: A,B in smem, K-major, 128B swizzle        (layout of mlp_tc.cu)
+//   variant 1: A,B in smem, K-major, no swizzle ("interleaved" 8x16B core matrices)
+//   variant 2: A in TMEM (bf16 pairs per 32-bit column), B in smem 128B swizzle
+#include "engine.h"
+#include "tc_common.cuh"
+
+namespace nerf {
+using namespace tc;
+
+__global__ void __launch_bounds__(128, 1)
+umma_probe_kernel(int variant, const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, int N, int K) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar_done;
+  __shared__ uint32_t tmem_base_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kblocks = K / 64;
+  uint8_t* sA = smem;                                   // kblocks x 16 KB
+  uint8_t* sB = smem + (size_t)kblocks * 16384;          // kblocks x (N*128) B
+
+  if (warp == 0) { tmem_alloc(&tmem_base_slot, 512); tmem_relinquish(); }
+  if (tid == 32) { mbar_init(&bar_done, 1); fence_barrier_init(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_slot;
+
+  // stage operands (fp32 -> bf16) into shared memory
+  for (int e = tid; e < 128 * K; e += 128) {
+    const int r = e / K, k = e % K;
+    const __nv_bfloat16 v = __float2bfloat16(A[e]);
+    uint32_t off;
+    if (variant == 1) off = (uint32_t)((k / 8) * (128 * 16) + r * 16 + (k % 8) * 2);
+    else off = (uint32_t)((k / 64) * 16384) + sw128_offset(r, (k % 64) / 8) + (k % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sA + off) = v;
+  }
+  for (int e = tid; e < N * K; e += 128) {
+    const int r = e / K, k = e % K;
+    const __nv_bfloat16 v = __float2bfloat16(B[e]);
+    uint32_t off;
+    if (variant == 1) off = (uint32_t)((k / 8) * (N * 16) + r * 16 + (k % 8) * 2);
+    else off = (uint32_t)((k / 64) * (N * 128)) + sw128_offset(r, (k % 64) / 8) + (k % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sB + off) = v;
+  }
+  if (variant == 2) {
+    // A into TMEM columns [256, 256 + K/2): thread = row, 2 bf16 per column (low half = even k)
+    const int row = warp * 32 + lane;
+    for (int c0 = 0; c0 < K / 2; c0 += 16) {
+      uint32_t v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = pack_bf16x2(A[row * K + 2 * (c0 + j)], A[row * K + 2 * (c0 + j) + 1]);
+      tmem_st16(tmem + ((uint32_t)(warp * 32) << 16) + 256 + c0, v);
+    }
+    tmem_wait_st();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  if (tid == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, N);
+    for (int ks = 0; ks < K / 16; ++ks) {
+      uint64_t ad, bd;
+      if (variant == 1) {
+        ad = make_smem_desc(smem_u32(sA) + ks * 2 * (128 * 16), 128 * 16, 128, kLayoutNone);
+        bd = make_smem_desc(smem_u32(sB) + ks * 2 * (N * 16), N * 16, 128, kLayoutNone);
+      } else {
+        const int kb = ks / 4, kk = ks % 4;
+        ad = make_smem_desc(smem_u32(sA) + kb * 16384 + kk * 32, 16, 1024, kLayoutSW128);
+        bd = make_smem_desc(smem_u32(sB) + kb * (N * 128) + kk * 32, 16, 1024, kLayoutSW128);
+      }
+      if (variant == 2) umma_ts(tmem, tmem + 256 + ks * 8, bd, idesc, ks > 0);
+      else umma_ss(tmem, ad, bd, idesc, ks > 0);
+    }
+    umma_commit(&bar_done);
+  }
+  mbar_wait(&bar_done, 0, 0x100 + variant);
+  tc_fence_after();
+  {
+    const int row = warp * 32 + lane;
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) D[row * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace nerf
+
+extern "C" int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K, void* stream) {
+  using namespace nerf;
+  if (M != 128 || N % 16 || N < 16 || N > 256 || K % 64 || K < 64 || K > 256 || variant < 0 || variant > 2) return NERF_E_INVALID;
+  const size_t smem = (size_t)(K / 64) * 16384 + (size_t)K * N * 2 + 1024;
+  cudaError_t e = cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return NERF_E_CUDA;
+  umma_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(variant, a, b, d, N, K);
+  return cudaGetLastError() == cudaSuccess ? NERF_OK : NERF_E_CUDA;
+}

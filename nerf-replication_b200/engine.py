@@ -1,0 +1,248 @@
+"""Engine: Python face of one ``NerfEngine`` handle (one per process / GPU).
+
+PyTorch is used for device memory and streams only: every method passes raw device pointers and the
+current CUDA stream to the C ABI (include/nerf_b200.h).  Nothing here computes on the host and there is
+no fallback path -- a missing library or GPU raises.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def _ptr(t, dtype=torch.float32, name="tensor", device=None):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise EngineError("%s must be a CUDA tensor" % name)
+    if t.dtype != dtype:
+        raise EngineError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if not t.is_contiguous():
+        raise EngineError("%s must be contiguous" % name)
+    if device is not None and t.device.index != device:
+        raise EngineError("%s is on cuda:%s, engine is on cuda:%d" % (name, t.device.index, device))
+    return t.data_ptr()
+
+
+class Engine:
+    """Owns a NerfEngine handle.  cfg keys mirror Renderer.__init__ (volume_renderer.py:9-24)."""
+
+    def __init__(self, n_samples=64, n_importance=128, white_bkgd=True, perturb=False, train_u=False,
+                 precision="bf16", t_near=2.0, t_far=6.0, seed=0, device=None):
+        if not torch.cuda.is_available():
+            raise EngineError("nerf_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.lib = L.load()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.cfg = L.NerfConfig()
+        self._set_cfg_fields(n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed)
+        h = C.c_void_p()
+        rc = self.lib.nerf_create(C.byref(self.cfg), self.device, C.byref(h))
+        if rc != 0:
+            raise EngineError("nerf_create failed (%d): %s" % (rc, self.lib.nerf_last_error(None).decode()))
+        self.h = h
+        self._flat = None
+
+    # -- plumbing -------------------------------------------------------------------------------
+    def _set_cfg_fields(self, n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed):
+        c = self.cfg
+        c.n_samples, c.n_importance = int(n_samples), int(n_importance)
+        c.white_bkgd, c.perturb, c.train_u = int(bool(white_bkgd)), int(bool(perturb)), int(bool(train_u))
+        c.precision = {"bf16": L.PRECISION_BF16, "fp32": L.PRECISION_FP32}[precision]
+        c.t_near, c.t_far, c.seed = float(t_near), float(t_far), int(seed)
+
+    @property
+    def precision(self):
+        return "fp32" if self.cfg.precision == L.PRECISION_FP32 else "bf16"
+
+    def configure(self, **kw):
+        c = self.cfg
+        cur = dict(n_samples=c.n_samples, n_importance=c.n_importance, white_bkgd=c.white_bkgd, perturb=c.perturb,
+                   train_u=c.train_u, precision=self.precision, t_near=c.t_near, t_far=c.t_far, seed=c.seed)
+        cur.update(kw)
+        self._set_cfg_fields(**cur)
+        self._check(self.lib.nerf_set_config(self.h, C.byref(self.cfg)))
+
+    def _check(self, rc):
+        if rc != 0:
+            raise EngineError("nerf_b200 error %d: %s" % (rc, self.lib.nerf_last_error(self.h).decode()))
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _p(self, t, dtype=torch.float32, name="tensor"):
+        return _ptr(t, dtype, name, self.device)
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.nerf_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self):
+        return int(self.lib.nerf_launch_count(self.h))
+
+    # -- parameters -----------------------------------------------------------------------------
+    def set_params(self, flat):
+        """flat: fp32 CUDA tensor [NERF_PARAMS_TOTAL] in state_dict order; kept alive by the engine."""
+        if flat.numel() != L.NERF_PARAMS_TOTAL:
+            raise EngineError("flat parameter buffer must have %d elements" % L.NERF_PARAMS_TOTAL)
+        self._check(self.lib.nerf_set_params(self.h, self._p(flat, name="flat"), self._stream()))
+        self._flat = flat
+
+    # -- stages ---------------------------------------------------------------------------------
+    def get_rays(self, c2w, H, W, focal, cx=None, cy=None, pixel_ids=None, pix0=0, n=None):
+        c2w = [float(x) for row in c2w[:3] for x in row[:4]]
+        arr = (C.c_double * 12)(*c2w)
+        if pixel_ids is not None:
+            n = pixel_ids.numel()
+        elif n is None:
+            n = H * W - pix0
+        o = torch.empty(n, 3, device="cuda:%d" % self.device)
+        d = torch.empty_like(o)
+        self._check(self.lib.nerf_get_rays(self.h, arr, H, W, float(focal), W / 2 if cx is None else cx,
+                                           H / 2 if cy is None else cy, self._p(pixel_ids, torch.int64, "pixel_ids"),
+                                           pix0, n, o.data_ptr(), d.data_ptr(), self._stream()))
+        return o, d
+
+    def stratified_t(self, n, S, jitter=None):
+        t = torch.empty(n, S, device="cuda:%d" % self.device)
+        self._check(self.lib.nerf_stratified_t(self.h, n, S, self._p(jitter, name="jitter"), t.data_ptr(), self._stream()))
+        return t
+
+    def freq_encode(self, x, n_freqs):
+        x = x.reshape(-1, 3)
+        out = torch.empty(x.shape[0], 3 + 6 * n_freqs, device=x.device)
+        self._check(self.lib.nerf_freq_encode(self.h, self._p(x, name="x"), x.shape[0], n_freqs, out.data_ptr(), self._stream()))
+        return out
+
+    def mlp_forward(self, which_net, pts, viewdirs, mask=None):
+        R, S, _ = pts.shape
+        raw = torch.empty(R, S, 4, device=pts.device)
+        if mask is not None:
+            mask = mask.to(torch.uint8).contiguous()
+        self._check(self.lib.nerf_mlp_forward(self.h, which_net, self._p(pts, name="pts"), self._p(viewdirs, name="viewdirs"),
+                                              self._p(mask, torch.uint8, "mask"), R, S, raw.data_ptr(), self._stream()))
+        return raw
+
+    def composite(self, raw, t, white_bkgd=True, want_weights=False):
+        n, S = t.shape
+        dev = raw.device
+        rgb, depth, acc = torch.empty(n, 3, device=dev), torch.empty(n, device=dev), torch.empty(n, device=dev)
+        w = torch.empty(n, S, device=dev) if want_weights else None
+        self._check(self.lib.nerf_composite(self.h, self._p(raw, name="raw"), self._p(t, name="t"), n, S, int(white_bkgd),
+                                            rgb.data_ptr(), depth.data_ptr(), acc.data_ptr(),
+                                            None if w is None else w.data_ptr(), self._stream()))
+        return rgb, depth, acc, w
+
+    def sample_pdf(self, raw_c, t_c, n_importance, u=None, cdf_in=None):
+        n, Nc = t_c.shape
+        Nf, dev = n_importance, t_c.device
+        out = dict(t_fine=torch.empty(n, Nf, device=dev),
+                   inds=torch.empty(n, Nf, dtype=torch.int64, device=dev),
+                   below=torch.empty(n, Nf, dtype=torch.int64, device=dev),
+                   above=torch.empty(n, Nf, dtype=torch.int64, device=dev),
+                   cdf=torch.empty(n, Nc - 1, device=dev),
+                   t_sorted=torch.empty(n, Nc + Nf, device=dev),
+                   sort_idx=torch.empty(n, Nc + Nf, dtype=torch.int32, device=dev))
+        self._check(self.lib.nerf_sample_pdf(self.h, self._p(raw_c, name="raw_c"), self._p(t_c, name="t_c"), n, Nc, Nf,
+                                             self._p(u, name="u"), self._p(cdf_in, name="cdf_in"),
+                                             out["t_fine"].data_ptr(), out["inds"].data_ptr(), out["below"].data_ptr(),
+                                             out["above"].data_ptr(), out["cdf"].data_ptr(), out["t_sorted"].data_ptr(),
+                                             out["sort_idx"].data_ptr(), self._stream()))
+        return out
+
+    # -- render ---------------------------------------------------------------------------------
+    def _render_out(self, n, dev, full):
+        t = dict(rgb=torch.empty(n, 3, device=dev), depth=torch.empty(n, device=dev))
+        if full:
+            t.update(acc=torch.empty(n, device=dev), rgb_coarse=torch.empty(n, 3, device=dev),
+                     depth_coarse=torch.empty(n, device=dev), acc_coarse=torch.empty(n, device=dev))
+        ro = L.NerfRenderOut()
+        for k, v in t.items():
+            setattr(ro, k, v.data_ptr())
+        return t, ro
+
+    def render_rays(self, rays_o, rays_d, jitter=None, u=None, full=False):
+        """rays_o/rays_d [n,3] fp32 CUDA -> dict of maps (rgb, depth[, acc, *_coarse])."""
+        n = rays_o.shape[0]
+        t, ro = self._render_out(n, rays_o.device, full)
+        self._check(self.lib.nerf_render_rays(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"), n,
+                                              self._p(jitter, name="jitter"), self._p(u, name="u"), C.byref(ro), self._stream()))
+        return t
+
+    def render_camera(self, c2w, H, W, focal, cx=None, cy=None, pix0=0, n=None, full=False):
+        n = H * W - pix0 if n is None else n
+        c2w = [float(x) for row in c2w[:3] for x in row[:4]]
+        t, ro = self._render_out(n, torch.device("cuda:%d" % self.device), full)
+        self._check(self.lib.nerf_render_camera(self.h, (C.c_double * 12)(*c2w), H, W, float(focal),
+                                                W / 2 if cx is None else cx, H / 2 if cy is None else cy, pix0, n,
+                                                C.byref(ro), self._stream()))
+        return t
+
+    def render_rays_host(self, rays_o, rays_d, rgb_out=None, depth_out=None):
+        """Host (CPU) tensors in, host tensors out: the end-to-end path with H2D/D2H inside the call."""
+        for x in (rays_o, rays_d):
+            if x.is_cuda or x.dtype != torch.float32 or not x.is_contiguous():
+                raise EngineError("render_rays_host takes contiguous fp32 CPU tensors")
+        n = rays_o.shape[0]
+        rgb = torch.empty(n, 3) if rgb_out is None else rgb_out
+        depth = torch.empty(n) if depth_out is None else depth_out
+        self._check(self.lib.nerf_render_rays_host(self.h, rays_o.data_ptr(), rays_d.data_ptr(), n, rgb.data_ptr(), depth.data_ptr()))
+        return rgb, depth
+
+    # -- training -------------------------------------------------------------------------------
+    def forward_backward(self, rays_o, rays_d, rgb_gt, flat_grad, jitter=None, u=None, grad_scale=1.0, want_rgb=False):
+        n = rays_o.shape[0]
+        loss = torch.empty((), device=rays_o.device)
+        rgb = torch.empty(n, 3, device=rays_o.device) if want_rgb else None
+        self._check(self.lib.nerf_forward_backward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"),
+                                                   self._p(rgb_gt, name="rgb_gt"), n, self._p(jitter, name="jitter"),
+                                                   self._p(u, name="u"), float(grad_scale), loss.data_ptr(),
+                                                   self._p(flat_grad, name="flat_grad"),
+                                                   None if rgb is None else rgb.data_ptr(), self._stream()))
+        return (loss, rgb) if want_rgb else loss
+
+    def train_forward(self, rays_o, rays_d, jitter=None, u=None):
+        n = rays_o.shape[0]
+        rgb, depth = torch.empty(n, 3, device=rays_o.device), torch.empty(n, device=rays_o.device)
+        self._check(self.lib.nerf_train_forward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"), n,
+                                                self._p(jitter, name="jitter"), self._p(u, name="u"), rgb.data_ptr(),
+                                                depth.data_ptr(), self._stream()))
+        return rgb, depth
+
+    def train_backward(self, rays_o, rays_d, d_rgb, d_depth, flat_grad, zero_grad=True):
+        n = rays_o.shape[0]
+        self._check(self.lib.nerf_train_backward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"), n,
+                                                 self._p(d_rgb, name="d_rgb"), self._p(d_depth, name="d_depth"),
+                                                 self._p(flat_grad, name="flat_grad"), int(zero_grad), self._stream()))
+
+    def clip_adam(self, flat_param, flat_grad, m, v, step, lr=5e-4, beta1=0.9, beta2=0.999, eps=1e-8, clip=40.0):
+        self._check(self.lib.nerf_clip_adam(self.h, self._p(flat_param, name="flat_param"), self._p(flat_grad, name="flat_grad"),
+                                            self._p(m, name="m"), self._p(v, name="v"), lr, beta1, beta2, eps, clip, int(step),
+                                            self._stream()))
+
+    # -- debug ----------------------------------------------------------------------------------
+    def umma_probe(self, variant, a, b):
+        M, K = a.shape
+        N = b.shape[0]
+        d = torch.zeros(M, N, device=a.device)
+        rc = self.lib.nerf_debug_umma_probe(variant, self._p(a, name="a"), self._p(b, name="b"), d.data_ptr(), M, N, K, self._stream())
+        if rc != 0:
+            raise EngineError("umma probe launch failed (%d)" % rc)
+        return d
+
+    def watchdog(self):
+        out = (C.c_uint * 8)()
+        self.lib.nerf_debug_tc_watchdog(out)
+        return list(out)
