@@ -83,6 +83,13 @@ int nerf_version(void);
 /* Number of engine kernels launched through this handle since creation (bench.py's gpu_launches). */
 int64_t nerf_launch_count(const NerfEngine* h);
 
+/* Kernel timing for bench.py's roofline line: while enabled, CUDA events bracket every fused-MLP launch on
+ * the stream it is launched on.  nerf_profile_read synchronises the device, returns the summed duration
+ * (ms), the number of bracketed launches and the MLP rows (sample evaluations) they processed since the
+ * last read, and resets the counters. */
+int nerf_profile_enable(NerfEngine* h, int on);
+int nerf_profile_read(NerfEngine* h, double* mlp_ms, int64_t* mlp_launches, int64_t* mlp_rows);
+
 /* ---- stage kernels (parity taps; each is also used by the fused calls) ------------------------- */
 /* a-B get_rays, src/datasets/nerf/blender.py:95-127.  c2w_host: 12 doubles (3x4 row-major).  pixel_ids
  * (device int64[n]) or NULL for the pixel range [pix0, pix0+n) in row-major order. */

@@ -54,6 +54,7 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   cudaDeviceSynchronize();
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
   if (h->wpack) cudaFree(h->wpack);
+  for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   for (int i = 0; i < 2; ++i) {
     if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
     if (h->hev[i]) cudaEventDestroy(h->hev[i]);
@@ -132,7 +133,33 @@ extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_
 
 static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep, cudaStream_t st) {
   if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_forward(h, net, src, raw, keep, st);
-  return mlp_tc_forward(h, net, src, raw, st);
+  if (h->profiling) cudaEventRecord(h->prof_event(), st);
+  const int rc = mlp_tc_forward(h, net, src, raw, st);
+  if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; }
+  return rc;
+}
+
+extern "C" int nerf_profile_enable(NerfEngine* h, int on) {
+  if (!h) return NERF_E_INVALID;
+  h->profiling = on != 0;
+  return NERF_OK;
+}
+
+extern "C" int nerf_profile_read(NerfEngine* h, double* mlp_ms, int64_t* mlp_launches, int64_t* mlp_rows) {
+  if (!h) return NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  NERF_CUDA_TRY(h, cudaDeviceSynchronize());
+  double ms = 0.0;
+  for (size_t i = 0; i + 1 < h->prof_used; i += 2) {
+    float t = 0.f;
+    NERF_CUDA_TRY(h, cudaEventElapsedTime(&t, h->prof_pool[i], h->prof_pool[i + 1]));
+    ms += t;
+  }
+  if (mlp_ms) *mlp_ms = ms;
+  if (mlp_launches) *mlp_launches = (int64_t)(h->prof_used / 2);
+  if (mlp_rows) *mlp_rows = h->prof_rows;
+  h->prof_used = 0; h->prof_rows = 0;
+  return NERF_OK;
 }
 
 extern "C" int nerf_mlp_forward(NerfEngine* h, int which_net, const float* pts, const float* viewdirs, const uint8_t* mask,

@@ -31,6 +31,16 @@ struct NerfEngine {
   void* pinned[2] = {nullptr, nullptr};
   size_t pinned_bytes = 0;
 
+  // optional event bracketing of the fused-MLP launches (nerf_profile_enable / nerf_profile_read)
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_pool;      // all events ever created (reused)
+  size_t prof_used = 0;                    // events handed out since the last read (pairs: begin, end)
+  int64_t prof_rows = 0;
+  cudaEvent_t prof_event() {
+    if (prof_used == prof_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); prof_pool.push_back(e); }
+    return prof_pool[prof_used++];
+  }
+
   int fail(int code, const std::string& m) { err = m; return code; }
 
   template <typename T>

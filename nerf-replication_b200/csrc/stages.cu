@@ -34,11 +34,10 @@ __global__ void get_rays_kernel(Camera cam, const int64_t* __restrict__ pixel_id
     double wx = cam.r64[0] * dx + cam.r64[1] * dy + cam.r64[2] * dz;
     double wy = cam.r64[3] * dx + cam.r64[4] * dy + cam.r64[5] * dz;
     double wz = cam.r64[6] * dx + cam.r64[7] * dy + cam.r64[8] * dz;
-    const double inv = 1.0 / sqrt(wx * wx + wy * wy + wz * wz);
-    // numpy divides (x / norm); multiplying by the reciprocal differs by <= 1 ulp(f64), invisible in fp32
-    rays_d[3 * i + 0] = (float)(wx * inv);
-    rays_d[3 * i + 1] = (float)(wy * inv);
-    rays_d[3 * i + 2] = (float)(wz * inv);
+    const double nrm = sqrt(wx * wx + wy * wy + wz * wz);   // numpy divides by the norm (blender.py:126)
+    rays_d[3 * i + 0] = (float)(wx / nrm);
+    rays_d[3 * i + 1] = (float)(wy / nrm);
+    rays_d[3 * i + 2] = (float)(wz / nrm);
     rays_o[3 * i + 0] = (float)cam.o64[0];
     rays_o[3 * i + 1] = (float)cam.o64[1];
     rays_o[3 * i + 2] = (float)cam.o64[2];

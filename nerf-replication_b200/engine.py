@@ -92,6 +92,15 @@ class Engine:
     def launch_count(self):
         return int(self.lib.nerf_launch_count(self.h))
 
+    def profile(self, on=True):
+        self._check(self.lib.nerf_profile_enable(self.h, int(on)))
+
+    def profile_read(self):
+        """-> (ms spent in fused-MLP launches, launches, MLP rows) since the last read; synchronises."""
+        ms, n, rows = C.c_double(), C.c_int64(), C.c_int64()
+        self._check(self.lib.nerf_profile_read(self.h, C.byref(ms), C.byref(n), C.byref(rows)))
+        return ms.value, n.value, rows.value
+
     # -- parameters -----------------------------------------------------------------------------
     def set_params(self, flat):
         """flat: fp32 CUDA tensor [NERF_PARAMS_TOTAL] in state_dict order; kept alive by the engine."""

@@ -1,0 +1,165 @@
+"""GPU parity of the non-MLP stage kernels (csrc/stages.cu) through the C ABI, each fed the oracle's
+upstream tensors (stage-wise parity).  Integer outputs are bit-exact; fp32 outputs are held
+to 1e-5 abs (north_star's fp32 tolerance) or tighter where stated."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from gpu_util import dev, make_engine, maxabs, state_dict_for
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5   # north_star: fp32 validation tolerance
+
+
+@pytest.fixture(scope="module")
+def eng(oracle):
+    e = make_engine(oracle, oracle.init_state_dict(0), "fp32")
+    yield e
+    e.close()
+
+
+def test_get_rays_matches_blender_dataset_math(eng, oracle):
+    g = load_golden("get_rays_100")
+    f = oracle.focal_from_fov(100)
+    o, d = eng.get_rays(g["c2w"], 100, 100, f, pixel_ids=dev(g["pix"]))
+    assert maxabs(o, g["rays_o"]) == 0.0
+    assert maxabs(d, g["rays_d"]) <= 1.2e-7          # <= 1 ulp(fp32) after the float64 -> float32 rounding
+    # full 800x800 view, row-major pixel order (blender.py:114-115), against the numpy restatement
+    c2w = oracle.lego_pose(3)
+    ro, rd = oracle.get_rays_np(c2w, 800, 800)
+    o, d = eng.get_rays(c2w, 800, 800, oracle.focal_from_fov(800))
+    assert maxabs(o, ro) == 0.0 and maxabs(d, rd) <= 1.2e-7
+    assert float((d.cpu() == torch.from_numpy(rd)).float().mean()) > 0.999
+    np.testing.assert_allclose(d.norm(dim=-1).cpu().numpy(), 1.0, atol=1e-6)
+
+
+@pytest.mark.parametrize("S", [64, 128, 7])
+def test_stratified_t_bit_exact(eng, oracle, S):
+    t = eng.stratified_t(33, S)
+    assert torch.equal(t.cpu(), oracle.stratified_t(33, S))
+    jit = torch.rand(33, S, generator=torch.Generator().manual_seed(S))
+    t = eng.stratified_t(33, S, jitter=jit.cuda())
+    assert torch.equal(t.cpu(), oracle.stratified_t(33, S, jit))
+
+
+def test_stratified_t_empty(eng):
+    assert eng.stratified_t(0, 64).shape == (0, 64)
+
+
+def test_freq_encode(eng, oracle):
+    g = load_golden("network_forward")
+    pe = eng.freq_encode(dev(g["pts"]).reshape(-1, 3), 10)
+    assert pe.shape == (320, 63)
+    assert maxabs(pe, g["pe_pts"]) <= 5e-7           # sinf/cosf are <= 2 ulp; arguments up to 3 * 512 rad
+    assert maxabs(eng.freq_encode(dev(g["viewdirs"]), 4), g["pe_dir"]) <= 5e-7
+    # large arguments: far plane 6 * 2^9
+    x = torch.tensor([[6.0, -6.0, 5.999], [0.0, 1e-8, -0.0]])
+    assert maxabs(eng.freq_encode(x.cuda(), 10), oracle.freq_encode(x, 10)) <= 5e-7
+
+
+@pytest.mark.parametrize("case", ["render_seed0_64rays", "render_sharp_64rays", "render_sharp_black_bkgd",
+                                  "render_sharp_128_256", "render_sharp_coarse_only"])
+def test_composite_from_oracle_raw(eng, case):
+    g = load_golden(case)
+    fine = int(g["n_importance"]) > 0
+    raw, t = (g["raw_fine"], g["depth_sorted"]) if fine else (g["raw_coarse"], g["t_coarse"])
+    rgb, depth, acc, w = eng.composite(dev(raw), dev(t), bool(g["white_bkgd"]), want_weights=True)
+    assert maxabs(rgb, g["rgb_map"]) <= TOL
+    assert maxabs(depth, g["depth_map"]) <= TOL
+    assert maxabs(acc, g["acc_map"]) <= TOL
+    assert maxabs(w, g["weights"]) <= 1e-6
+    if fine:   # coarse-pass maps (the opt-in extension of the output dict)
+        rgb, depth, acc, _ = eng.composite(dev(g["raw_coarse"]), dev(g["t_coarse"]), bool(g["white_bkgd"]))
+        assert maxabs(rgb, g["rgb_map_coarse"]) <= TOL and maxabs(depth, g["depth_map_coarse"]) <= TOL
+        assert maxabs(acc, g["acc_map_coarse"]) <= TOL
+
+
+def test_composite_edge_cases(eng, oracle):
+    # empty input, sigma == 0 everywhere (alpha 0, white background), opaque first sample, S not a multiple of 32
+    assert eng.composite(torch.empty(0, 64, 4).cuda(), torch.empty(0, 64).cuda())[0].shape == (0, 3)
+    t = oracle.stratified_t(5, 70)
+    raw = torch.zeros(5, 70, 4)
+    raw[..., 3] = -1.0
+    rgb, depth, acc, _ = eng.composite(raw.cuda(), t.cuda(), True)
+    assert maxabs(rgb, torch.ones(5, 3)) == 0.0 and maxabs(acc, torch.zeros(5)) == 0.0
+    raw[..., 3] = 1e4
+    raw[..., :3] = 2.0
+    ref = oracle.composite(raw, t, True)
+    out = eng.composite(raw.cuda(), t.cuda(), True, want_weights=True)
+    for a, b in zip(out, ref):
+        assert maxabs(a, b) <= TOL
+    g = torch.Generator().manual_seed(5)
+    raw = torch.randn(9, 70, 4, generator=g) * 4
+    ref = oracle.composite(raw, t[:1].expand(9, 70).contiguous(), False)
+    out = eng.composite(raw.cuda(), t[:1].expand(9, 70).contiguous().cuda(), False, want_weights=True)
+    for a, b in zip(out, ref):
+        assert maxabs(a, b) <= TOL
+
+
+@pytest.mark.parametrize("case", ["render_seed0_64rays", "render_sharp_64rays", "render_sharp_128_256"])
+def test_sample_pdf_indices_bit_exact_with_oracle_cdf(eng, case):
+    """searchsorted(right=True) + the reference's clamp at Nc-3, merge sort."""
+    g = load_golden(case)
+    Nf = int(g["n_importance"])
+    out = eng.sample_pdf(dev(g["raw_coarse"]), dev(g["t_coarse"]), Nf, cdf_in=dev(g["cdf"]))
+    for k in ("inds", "below", "above"):
+        assert torch.equal(out[k].cpu(), torch.from_numpy(g[k])), k
+    assert torch.equal(out["t_fine"].cpu(), torch.from_numpy(g["t_fine"]))     # same rn op sequence as torch
+    assert torch.equal(out["t_sorted"].cpu(), torch.from_numpy(g["depth_sorted"]))
+    idx = out["sort_idx"].cpu().long()
+    cat = torch.cat([torch.from_numpy(g["t_coarse"]), torch.from_numpy(g["t_fine"])], 1)
+    assert torch.equal(torch.gather(cat, 1, idx), torch.from_numpy(g["depth_sorted"]))
+    assert torch.equal(torch.sort(idx, -1).values, torch.arange(idx.shape[1]).expand_as(idx))   # a permutation
+
+
+@pytest.mark.parametrize("case", ["render_seed0_64rays", "render_sharp_64rays", "render_sharp_128_256"])
+def test_sample_pdf_own_cdf(eng, case):
+    g = load_golden(case)
+    Nf = int(g["n_importance"])
+    out = eng.sample_pdf(dev(g["raw_coarse"]), dev(g["t_coarse"]), Nf)
+    assert maxabs(out["cdf"], g["cdf"]) <= 1e-6
+    flips = float((out["inds"].cpu() != torch.from_numpy(g["inds"])).float().mean())
+    assert flips <= 5e-3, "index flip rate %g" % flips                # O(1e-4) expected (SURVEY H1 iv)
+    same = out["inds"].cpu() == torch.from_numpy(g["inds"])
+    assert maxabs(out["t_fine"].cpu()[same], torch.from_numpy(g["t_fine"])[same]) <= 1e-4
+    ts = out["t_sorted"].cpu()
+    assert (ts[:, 1:] >= ts[:, :-1]).all()
+
+
+def test_sample_pdf_explicit_u_and_ragged(eng, oracle):
+    """train-mode u (volume_renderer.py:143-144) injected; Nc/Nf not multiples of 32; u = 0 and u -> 1."""
+    gen = torch.Generator().manual_seed(11)
+    n, Nc, Nf = 19, 40, 77
+    t_c = oracle.stratified_t(n, Nc, torch.rand(n, Nc, generator=gen))
+    raw = torch.randn(n, Nc, 4, generator=gen) * 3
+    u = torch.rand(n, Nf, generator=gen)
+    u[:, 0], u[:, 1] = 0.0, 1.0 - 2 ** -24
+    taps = {}
+    t_f = oracle.sample_pdf(torch.relu(raw[..., 3]), t_c, Nf, u, taps=taps)
+    out = eng.sample_pdf(raw.cuda(), t_c.cuda(), Nf, u=u.cuda(), cdf_in=taps["cdf"].cuda())
+    assert torch.equal(out["inds"].cpu(), taps["inds"]) and torch.equal(out["below"].cpu(), taps["below"])
+    assert torch.equal(out["above"].cpu(), taps["above"])
+    assert torch.equal(out["t_fine"].cpu(), t_f)
+    assert torch.equal(out["t_sorted"].cpu(), torch.sort(torch.cat([t_c, t_f], 1), -1).values)
+
+
+def test_full_size_properties(eng, oracle):
+    """BASELINE C2 size (one 800-px row band x 64+128): sortedness, permutation, partition of unity."""
+    n = 800 * 40
+    gen = torch.Generator().manual_seed(2)
+    raw_c = (torch.randn(n, 64, 4, generator=gen) * 2).cuda()
+    t_c = eng.stratified_t(n, 64)
+    out = eng.sample_pdf(raw_c, t_c, 128)
+    ts = out["t_sorted"]
+    assert bool((ts[:, 1:] >= ts[:, :-1]).all())
+    assert float(ts.min()) >= 2.0 and float(ts.max()) <= 6.0
+    idx = out["sort_idx"].long()
+    assert torch.equal(torch.sort(idx, -1).values, torch.arange(192, device="cuda").expand_as(idx))
+    assert int(out["below"].max()) <= 61 and int(out["above"].max()) <= 61 and int(out["inds"].max()) <= 63
+    raw_f = (torch.randn(n, 192, 4, generator=gen) * 2).cuda()
+    rgb_w, depth, acc, w = eng.composite(raw_f, ts, True, want_weights=True)
+    rgb_b, _, _, _ = eng.composite(raw_f, ts, False)
+    assert maxabs(rgb_b + (1 - acc)[:, None], rgb_w) <= 1e-6
+    assert float(acc.max()) <= 1 + 1e-5 and float(w.min()) >= 0
+    assert maxabs(w.sum(-1), acc) <= 1e-5

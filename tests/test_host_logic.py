@@ -1,0 +1,111 @@
+"""Host-side logic of the drop-in classes (no GPU): config precedence, Network parameter surface,
+sharding, LR schedule, and the data-parallel gradient exchange on world_size-2 gloo."""
+import os
+import socket
+from types import SimpleNamespace
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from nerf_replication_b200 import config as C
+from nerf_replication_b200.network import Network
+from nerf_replication_b200.renderer import Renderer
+from nerf_replication_b200.trainer import allreduce_mean_, exponential_lr, shard_range
+
+
+def test_knob_precedence():
+    cfg = C.default_cfg()
+    assert C.knob(cfg, "N_samples", 7) == 64            # falls back to task_arg
+    cfg.N_samples = 32
+    assert C.knob(cfg, "N_samples", 7) == 32            # top-level wins (volume_renderer.py:14)
+    assert C.knob(cfg, "weights_threshold", 0.25) == 0.25
+    assert C.knob({"task_arg": {"N_importance": 5}}, "N_importance", 128) == 5
+
+
+def test_renderer_reads_reference_keys():
+    cfg = C.default_cfg()
+    r = Renderer(net=None, cfg=cfg)
+    assert (r.N_samples, r.N_importance, r.white_bkgd) == (64, 128, True)
+    assert r.perturb is False                            # task != "train" forces perturb off (:21-22)
+    cfg.task = "train"
+    assert Renderer(net=None, cfg=cfg).perturb is True
+    cfg.fast_sampling = True
+    with pytest.raises(NotImplementedError):
+        Renderer(net=None, cfg=cfg)
+
+
+def test_network_surface_matches_reference(oracle):
+    torch.manual_seed(0)
+    net = Network(cfg=C.default_cfg())
+    sd = net.state_dict()
+    assert list(sd.keys()) == oracle.state_dict_keys()
+    ref = oracle.init_state_dict(0)
+    for k in sd:
+        assert torch.equal(sd[k], ref[k]), k             # same registration order -> bit-identical init
+    assert (net.input_ch, net.input_ch_views, net.N_samples, net.N_importance, net.chunk) == (63, 27, 64, 128, 512)
+    with pytest.raises(RuntimeError):
+        net.flat_params                                  # no CPU path
+    bad = C.default_cfg()
+    bad.network.nerf.W = 128
+    with pytest.raises(NotImplementedError):
+        Network(cfg=bad)
+
+
+def test_nerf_module_forward_is_the_oracle_mlp(oracle):
+    torch.manual_seed(0)
+    net = Network(cfg=C.default_cfg())
+    x = torch.randn(16, 90)
+    with torch.no_grad():
+        torch.testing.assert_close(net.model_fine(x), oracle.nerf_mlp(oracle.init_state_dict(0), "model_fine", x))
+
+
+def test_shard_range_partitions():
+    for n in (0, 1, 7, 800, 640000):
+        for w in (1, 2, 3, 8):
+            spans = [shard_range(n, r, w) for r in range(w)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [e - b for b, e in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_exponential_lr():
+    assert exponential_lr(5e-4, 0) == 5e-4
+    assert abs(exponential_lr(5e-4, 500) - 5e-5) < 1e-12
+    assert abs(exponential_lr(5e-4, 1) - 5e-4 * 0.1 ** (1 / 500)) < 1e-15
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _ddp_worker(rank, world, port, out):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = torch.arange(1191688, dtype=torch.float32) * (rank + 1)
+    allreduce_mean_(g)
+    out[rank] = (g[:8].clone(), float(g[-1]))
+    b, e = shard_range(800, rank, world)
+    t = torch.tensor([e - b], dtype=torch.int64)
+    dist.all_reduce(t)
+    out[world + rank] = int(t)
+    dist.destroy_process_group()
+
+
+def test_gradient_allreduce_world2_gloo():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_ddp_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    base = torch.arange(8, dtype=torch.float32)
+    for r in range(world):
+        head, last = out[r]
+        torch.testing.assert_close(head, base * 1.5)     # mean of g and 2g
+        assert last == 1191687 * 1.5
+        assert out[world + r] == 800                      # row bands cover the image exactly once
