@@ -110,6 +110,7 @@ static Camera make_camera(const double* c2w, int H, int W, double focal, double 
 
 extern "C" int nerf_get_rays(NerfEngine* h, const double* c2w_host, int H, int W, double focal, double cx, double cy,
                              const int64_t* pixel_ids, int64_t pix0, int64_t n, float* rays_o, float* rays_d, void* stream) {
+  if (h && n == 0) return NERF_OK;
   if (!h || !c2w_host || !rays_o || !rays_d || n < 0 || H <= 0 || W <= 0) return h ? h->fail(NERF_E_INVALID, "nerf_get_rays: bad argument") : NERF_E_INVALID;
   if (!pixel_ids && (pix0 < 0 || pix0 + n > (int64_t)H * W)) return h->fail(NERF_E_INVALID, "nerf_get_rays: pixel range outside the image");
   cudaSetDevice(h->device);
@@ -118,6 +119,7 @@ extern "C" int nerf_get_rays(NerfEngine* h, const double* c2w_host, int H, int W
 }
 
 extern "C" int nerf_stratified_t(NerfEngine* h, int64_t n, int S, const float* jitter, float* t, void* stream) {
+  if (h && n == 0) return NERF_OK;
   if (!h || !t || n < 0 || S < 2) return h ? h->fail(NERF_E_INVALID, "nerf_stratified_t: bad argument") : NERF_E_INVALID;
   cudaSetDevice(h->device);
   launch_stratified_t(h, n, S, jitter, false, 0, t, (cudaStream_t)stream);
@@ -125,6 +127,7 @@ extern "C" int nerf_stratified_t(NerfEngine* h, int64_t n, int S, const float* j
 }
 
 extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, float* out, void* stream) {
+  if (h && m == 0) return NERF_OK;
   if (!h || !x || !out || m < 0 || n_freqs < 0 || n_freqs > 16) return h ? h->fail(NERF_E_INVALID, "nerf_freq_encode: bad argument") : NERF_E_INVALID;
   cudaSetDevice(h->device);
   launch_freq_encode(h, x, m, n_freqs, out, (cudaStream_t)stream);
@@ -166,6 +169,7 @@ extern "C" int nerf_mlp_forward(NerfEngine* h, int which_net, const float* pts, 
                                 int64_t R, int S, float* raw, void* stream) {
   if (!h) return NERF_E_INVALID;
   if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_mlp_forward before nerf_set_params");
+  if (R == 0) return NERF_OK;
   if (!pts || !viewdirs || !raw || R < 0 || S < 1 || (which_net != NERF_NET_COARSE && which_net != NERF_NET_FINE))
     return h->fail(NERF_E_INVALID, "nerf_mlp_forward: bad argument");
   cudaSetDevice(h->device);
@@ -177,6 +181,7 @@ extern "C" int nerf_mlp_forward(NerfEngine* h, int which_net, const float* pts, 
 
 extern "C" int nerf_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white_bkgd, float* rgb,
                               float* depth, float* acc, float* weights, void* stream) {
+  if (h && n == 0) return NERF_OK;
   if (!h || !raw || !t || n < 0 || S < 1) return h ? h->fail(NERF_E_INVALID, "nerf_composite: bad argument") : NERF_E_INVALID;
   cudaSetDevice(h->device);
   launch_composite(h, raw, t, n, S, white_bkgd, rgb, depth, acc, weights, (cudaStream_t)stream);
@@ -186,6 +191,7 @@ extern "C" int nerf_composite(NerfEngine* h, const float* raw, const float* t, i
 extern "C" int nerf_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf, const float* u,
                                const float* cdf_in, float* t_fine, int64_t* inds, int64_t* below, int64_t* above,
                                float* cdf_out, float* t_sorted, int32_t* sort_idx, void* stream) {
+  if (h && n == 0) return NERF_OK;
   if (!h || !raw_c || !t_c || n < 0) return h ? h->fail(NERF_E_INVALID, "nerf_sample_pdf: bad argument") : NERF_E_INVALID;
   cudaSetDevice(h->device);
   int rc = launch_sample_pdf(h, raw_c, t_c, n, Nc, Nf, u, false, 0, cdf_in, t_fine, inds, below, above, cdf_out, t_sorted,
@@ -262,6 +268,7 @@ extern "C" int nerf_render_rays(NerfEngine* h, const float* rays_o, const float*
                                 const float* u, const NerfRenderOut* out, void* stream) {
   if (!h) return NERF_E_INVALID;
   if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_rays before nerf_set_params");
+  if (n == 0) return NERF_OK;
   if (!rays_o || !rays_d || !out || n < 0) return h->fail(NERF_E_INVALID, "nerf_render_rays: bad argument");
   cudaSetDevice(h->device);
   const int Nc = h->cfg.n_samples, Nf = h->cfg.n_importance;
@@ -278,6 +285,7 @@ extern "C" int nerf_render_camera(NerfEngine* h, const double* c2w_host, int H, 
                                   int64_t pix0, int64_t n, const NerfRenderOut* out, void* stream) {
   if (!h) return NERF_E_INVALID;
   if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_camera before nerf_set_params");
+  if (n == 0) return NERF_OK;
   if (!c2w_host || !out || n < 0 || pix0 < 0 || pix0 + n > (int64_t)H * W) return h->fail(NERF_E_INVALID, "nerf_render_camera: bad argument");
   cudaSetDevice(h->device);
   const Camera cam = make_camera(c2w_host, H, W, focal, cx, cy);
@@ -299,6 +307,7 @@ extern "C" int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, co
                                      float* rgb_host, float* depth_host) {
   if (!h) return NERF_E_INVALID;
   if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_render_rays_host before nerf_set_params");
+  if (n == 0) return NERF_OK;
   if (!rays_o_host || !rays_d_host || !rgb_host || !depth_host || n < 0) return h->fail(NERF_E_INVALID, "nerf_render_rays_host: bad argument");
   cudaSetDevice(h->device);
   const int nslots = h->cfg.precision == NERF_PRECISION_FP32 ? 1 : 2;

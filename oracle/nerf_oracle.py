@@ -103,7 +103,7 @@ def get_rays_np(c2w, H, W, pixel_ids=None, camera_angle_x=CAMERA_ANGLE_X):
     rays_d = (np.asarray(c2w)[:3, :3] @ dirs.T).T                               # :125
     rays_d = rays_d / np.linalg.norm(rays_d, axis=-1, keepdims=True)           # :126
     rays_o = np.broadcast_to(np.asarray(c2w)[:3, 3], rays_d.shape).copy()       # :127
-    return rays_o.astype(np.float32), rays_d.astype(np.float32)
+    return np.ascontiguousarray(rays_o, dtype=np.float32), np.ascontiguousarray(rays_d, dtype=np.float32)
 
 
 # ----------------------------------------------------------------------------------------------

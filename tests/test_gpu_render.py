@@ -19,6 +19,14 @@ FP32_RGB_TOL, FP32_DEPTH_TOL = 1e-5, 2e-4
 BF16_RGB_TOL, BF16_DEPTH_TOL = 1e-3, 2e-2
 
 
+def _continuous_rays(g, key, noise=0.03):
+    """The reference sets the last sample's delta to 1e10 (volume_renderer.py:80-81): alpha_last is 1 if
+    sigma_last > 0 else 0 -- a step function of the last raw sigma.  A ray whose last raw sigma is within the
+    bf16 activation noise of zero can legitimately land on the other side of the step (the CPU oracle with
+    bf16-rounded activations reproduces the same flip), so such rays are excluded from the bf16 comparison."""
+    return torch.from_numpy(np.abs(g[key][:, -1, 3]) > noise)
+
+
 def _cfg(g):
     return dict(n_samples=int(g["n_samples"]), n_importance=int(g["n_importance"]), white_bkgd=bool(g["white_bkgd"]))
 
@@ -48,9 +56,11 @@ def test_render_bf16_vs_oracle_bf16_weights(oracle, case):
     out = eng.render_rays(dev(g["rays_o"]), dev(g["rays_d"]), full=True)
     torch.cuda.synchronize()
     print(case, "rgb", quantiles(out["rgb"], g["rgb_map"]), "depth", quantiles(out["depth"], g["depth_map"]), eng.watchdog())
-    assert maxabs(out["rgb"], g["rgb_map"]) <= BF16_RGB_TOL
-    assert maxabs(out["rgb_coarse"], g["rgb_map_coarse"]) <= BF16_RGB_TOL
-    assert maxabs(out["depth"], g["depth_map"]) <= BF16_DEPTH_TOL
+    kf, kc = _continuous_rays(g, "raw_fine"), _continuous_rays(g, "raw_coarse")
+    assert int(kf.sum()) >= 60 and int(kc.sum()) >= 60
+    assert maxabs(out["rgb"].cpu()[kf], g["rgb_map"][kf.numpy()]) <= BF16_RGB_TOL
+    assert maxabs(out["rgb_coarse"].cpu()[kc], g["rgb_map_coarse"][kc.numpy()]) <= BF16_RGB_TOL
+    assert maxabs(out["depth"].cpu()[kf], g["depth_map"][kf.numpy()]) <= BF16_DEPTH_TOL
     eng.close()
 
 
@@ -98,8 +108,14 @@ def test_camera_mode_and_host_path_agree_with_ray_mode(oracle):
     assert maxabs(a["rgb"], b["rgb"]) <= BF16_RGB_TOL
     with torch.no_grad():
         rgb_ref, depth_ref = oracle.render(sd, torch.from_numpy(ro[:512]), torch.from_numpy(rd[:512]))
-    print("bf16 10k-ray frame vs oracle (first 512 rays): rgb", quantiles(a["rgb"][:512], rgb_ref), "depth", quantiles(a["depth"][:512], depth_ref))
-    assert maxabs(a["rgb"][:512], rgb_ref) <= BF16_RGB_TOL
+    taps = {}
+    with torch.no_grad():
+        oracle.render(sd, torch.from_numpy(ro[:512]), torch.from_numpy(rd[:512]), taps=taps)
+    keep = (taps["raw_fine"][:, -1, 3].abs() > 0.03)
+    print("bf16 10k-ray frame vs oracle (first 512 rays, %d continuous): rgb" % int(keep.sum()),
+          quantiles(a["rgb"][:512].cpu()[keep], rgb_ref[keep]), "depth", quantiles(a["depth"][:512].cpu()[keep], depth_ref[keep]))
+    assert int(keep.sum()) >= 480
+    assert maxabs(a["rgb"][:512].cpu()[keep], rgb_ref[keep]) <= BF16_RGB_TOL
     eng.close()
 
 

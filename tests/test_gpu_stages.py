@@ -118,11 +118,16 @@ def test_sample_pdf_own_cdf(eng, case):
     g = load_golden(case)
     Nf = int(g["n_importance"])
     out = eng.sample_pdf(dev(g["raw_coarse"]), dev(g["t_coarse"]), Nf)
-    assert maxabs(out["cdf"], g["cdf"]) <= 1e-6
+    # alpha = 1 - exp(-sigma delta) cancels: one ulp of exp() (the CPU libm and a correctly rounded exp differ in
+    # ~2% of calls) is 6e-5 relative in a pdf bin when sigma delta ~ 1e-3 -- hence 5e-5 on the cdf, not 1e-6.
+    assert maxabs(out["cdf"], g["cdf"]) <= 5e-5
     flips = float((out["inds"].cpu() != torch.from_numpy(g["inds"])).float().mean())
     assert flips <= 5e-3, "index flip rate %g" % flips                # O(1e-4) expected (SURVEY H1 iv)
     same = out["inds"].cpu() == torch.from_numpy(g["inds"])
-    assert maxabs(out["t_fine"].cpu()[same], torch.from_numpy(g["t_fine"])[same]) <= 1e-4
+    # inverse CDF divides by the bin mass: near-empty bins (w = 0 + 1e-5) amplify the cdf noise by up to 1e2
+    assert maxabs(out["t_fine"].cpu()[same], torch.from_numpy(g["t_fine"])[same]) <= 2e-3
+    d = (out["t_fine"].cpu()[same] - torch.from_numpy(g["t_fine"])[same]).abs()
+    assert float(torch.quantile(d, 0.9)) <= 1e-5
     ts = out["t_sorted"].cpu()
     assert (ts[:, 1:] >= ts[:, :-1]).all()
 
