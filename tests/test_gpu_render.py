@@ -56,11 +56,15 @@ def test_render_bf16_vs_oracle_bf16_weights(oracle, case):
     out = eng.render_rays(dev(g["rays_o"]), dev(g["rays_d"]), full=True)
     torch.cuda.synchronize()
     print(case, "rgb", quantiles(out["rgb"], g["rgb_map"]), "depth", quantiles(out["depth"], g["depth_map"]), eng.watchdog())
+    # every ray must be within tolerance unless it sits on the alpha_last step (see _continuous_rays);
+    # at most 10% of the rays may use that exemption
     kf, kc = _continuous_rays(g, "raw_fine"), _continuous_rays(g, "raw_coarse")
-    assert int(kf.sum()) >= 60 and int(kc.sum()) >= 60
-    assert maxabs(out["rgb"].cpu()[kf], g["rgb_map"][kf.numpy()]) <= BF16_RGB_TOL
-    assert maxabs(out["rgb_coarse"].cpu()[kc], g["rgb_map_coarse"][kc.numpy()]) <= BF16_RGB_TOL
-    assert maxabs(out["depth"].cpu()[kf], g["depth_map"][kf.numpy()]) <= BF16_DEPTH_TOL
+    e_rgb = (out["rgb"].cpu() - torch.from_numpy(g["rgb_map"])).abs().amax(-1)
+    e_rgb_c = (out["rgb_coarse"].cpu() - torch.from_numpy(g["rgb_map_coarse"])).abs().amax(-1)
+    e_dep = (out["depth"].cpu() - torch.from_numpy(g["depth_map"])).abs()
+    bad_f, bad_c, bad_d = e_rgb > BF16_RGB_TOL, e_rgb_c > BF16_RGB_TOL, e_dep > BF16_DEPTH_TOL
+    assert not (bad_f & kf).any() and not (bad_c & kc).any() and not (bad_d & kf).any()
+    assert int(bad_f.sum()) + int(bad_c.sum()) + int(bad_d.sum()) <= 6, (int(bad_f.sum()), int(bad_c.sum()), int(bad_d.sum()))
     eng.close()
 
 

@@ -21,33 +21,45 @@ def _per_tensor(oracle, flat):
     return out
 
 
-@pytest.mark.parametrize("sharp", [True, False])
-def test_gradients_match_reference_autograd(oracle, sharp):
-    sd = oracle.init_state_dict(0, sharp=sharp)
+@pytest.mark.parametrize("weights", ["fog", "sharp", "seed0"])
+def test_gradients_match_reference_autograd(oracle, weights):
+    """Engine gradients vs torch autograd on the oracle (the reference graph incl. the un-detached t_fine path).
+    fine net: 1e-3 of each tensor's max (or the fp32 noise floor where that is larger).
+    coarse net: its only signal is d loss / d t_fine through the inverse CDF.  With near-empty bins (seed0 /
+    sharp weights) that gradient is noise-dominated in fp32 -- the oracle itself moves by 20%..500% between fp32
+    and fp64 (measured: oracle.grads_fp64) -- so there the bound is the oracle's own fp32-vs-fp64 distance;
+    the "fog" weights (sigma ~ 1 everywhere, smooth CDF) are well conditioned and held to 2e-2 of max."""
+    sd = {"fog": oracle.fog_state_dict(0), "sharp": oracle.init_state_dict(0, sharp=True), "seed0": oracle.init_state_dict(0)}[weights]
     n = 32
     o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, n, 100, 100)
     tr = oracle.Trainer(sd)
     loss_ref = tr.forward_backward(o, d, gt)
     g_ref = tr.grads_flat()
+    _, g64 = oracle.grads_fp64(sd, o, d, gt)
     eng = make_engine(oracle, sd, "fp32")
     grad = torch.zeros(1191688, device="cuda")
     loss = eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad)
     torch.cuda.synchronize()
     assert abs(float(loss) - float(loss_ref)) <= 1e-6 * float(loss_ref)
-    if sharp:
+    if weights == "sharp":
         g = load_golden("train_sharp_32rays")          # the unmodified reference's own first-step loss
         assert abs(float(loss) - g["losses"][0]) <= 1e-5 * g["losses"][0]
-    ref_t, got_t = _per_tensor(oracle, g_ref), _per_tensor(oracle, grad.cpu())
+    ref_t, got_t, f64_t = _per_tensor(oracle, g_ref), _per_tensor(oracle, grad.cpu()), _per_tensor(oracle, g64)
+    bad = []
     for k in ref_t:
         scale = float(ref_t[k].abs().max())
         if k.startswith("model.") and any(s in k for s in ("views_linears", "feature_linear", "rgb_linear")):
             assert scale == 0.0 and float(got_t[k].abs().max()) == 0.0, k      # exactly-zero grads (fact 8)
             continue
         assert scale > 0, k
-        # fine net: 1e-3 of the tensor's max; coarse net: its only signal is d loss / d t_fine through the
-        # inverse CDF (tiny denominators) -- 2e-2 of max (fp32 reassociation in a 1e3-conditioned path)
-        tol = (2e-2 if k.startswith("model.") else 1e-3) * scale
-        assert maxabs(got_t[k], ref_t[k]) <= tol, (k, maxabs(got_t[k], ref_t[k]), scale)
+        noise = maxabs(ref_t[k], f64_t[k])                 # how far fp32 round-off alone moves this tensor
+        coarse = k.startswith("model.")
+        fixed = (2e-2 if coarse else 1e-3) * scale
+        tol = fixed if (coarse and weights == "fog") else max(fixed, 1.5 * noise)
+        err = maxabs(got_t[k], ref_t[k])
+        if err > tol:
+            bad.append((k, err, tol, scale, noise))
+    assert not bad, bad
     eng.close()
 
 
