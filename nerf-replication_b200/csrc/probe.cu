@@ -95,10 +95,83 @@ umma_probe_kernel(int variant, const float* __restrict__ A, const float* __restr
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
+// variant 3: CTA pair (cluster of 2, tcgen05 cta_group::2): D[256 x N] = A[256 x K] * B[N x K]^T.
+// CTA r stages A rows [128r, 128r+128) and B rows [N/2 r, N/2 r + N/2) (both K-major, 128B swizzle) at the SAME
+// shared-memory offsets; the leader (rank 0) issues M=256 MMAs; the commit is multicast to both CTAs; each CTA
+// reads its 128 accumulator rows from its own TMEM.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+umma_probe2_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, int N, int K) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar_done, bar_ready;
+  __shared__ uint32_t tmem_base_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int kblocks = K / 64, Nh = N / 2;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + (size_t)kblocks * 16384;
+
+  if (tid == 32) { mbar_init(&bar_done, 1); mbar_init(&bar_ready, 256); fence_barrier_init(); }
+  cluster_sync_all();
+  if (warp == 0) { tmem_alloc2(&tmem_base_slot, 512); tmem_relinquish2(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_slot;
+
+  for (int e = tid; e < 128 * K; e += 128) {
+    const int r = e / K, k = e % K;
+    const uint32_t off = (uint32_t)((k / 64) * 16384) + sw128_offset(r, (k % 64) / 8) + (k % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sA + off) = __float2bfloat16(A[(size_t)(rank * 128 + r) * K + k]);
+  }
+  for (int e = tid; e < Nh * K; e += 128) {
+    const int r = e / K, k = e % K;
+    const uint32_t off = (uint32_t)((k / 64) * (Nh * 128)) + sw128_offset(r, (k % 64) / 8) + (k % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sB + off) = __float2bfloat16(B[(size_t)(rank * Nh + r) * K + k]);
+  }
+  fence_proxy_async_smem();
+  mbar_arrive_cluster(mapa_u32(smem_u32(&bar_ready), 0));      // 128 threads x 2 CTAs arrive on the leader's barrier
+
+  if (rank == 0 && tid == 0) {
+    mbar_wait_cluster(&bar_ready, 0, 0x200);
+    tc_fence_after();
+    const uint32_t idesc = make_idesc_bf16(256, N);
+    for (int ks = 0; ks < K / 16; ++ks) {
+      const int kb = ks / 4, kk = ks % 4;
+      const uint64_t ad = make_smem_desc(smem_u32(sA) + kb * 16384 + kk * 32, 16, 1024, kLayoutSW128);
+      const uint64_t bd = make_smem_desc(smem_u32(sB) + kb * (Nh * 128) + kk * 32, 16, 1024, kLayoutSW128);
+      umma_ss2(tmem, ad, bd, idesc, ks > 0);
+    }
+    umma_commit2(&bar_done, 0x3);
+  }
+  mbar_wait(&bar_done, 0, 0x103);
+  tc_fence_after();
+  {
+    const int row = warp * 32 + lane;
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) D[(size_t)(rank * 128 + row) * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 0) tmem_dealloc2(tmem, 512);
+}
+
 }  // namespace nerf
 
 extern "C" int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K, void* stream) {
   using namespace nerf;
+  if (variant == 3) {
+    if (M != 256 || N % 32 || N < 32 || N > 256 || K % 64 || K < 64 || K > 256) return NERF_E_INVALID;
+    const size_t smem2 = (size_t)(K / 64) * 16384 + (size_t)K * (N / 2) * 2 + 1024;
+    if (cudaFuncSetAttribute(umma_probe2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2) != cudaSuccess) return NERF_E_CUDA;
+    umma_probe2_kernel<<<2, 128, smem2, (cudaStream_t)stream>>>(a, b, d, N, K);
+    return cudaGetLastError() == cudaSuccess ? NERF_OK : NERF_E_CUDA;
+  }
   if (M != 128 || N % 16 || N < 16 || N > 256 || K % 64 || K < 64 || K > 256 || variant < 0 || variant > 2) return NERF_E_INVALID;
   const size_t smem = (size_t)(K / 64) * 16384 + (size_t)K * N * 2 + 1024;
   cudaError_t e = cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -25,6 +25,20 @@ def test_umma_probe(oracle, variant, N, K):
     eng.close()
 
 
+@pytest.mark.parametrize("N,K", [(256, 64), (256, 256), (128, 128), (64, 64)])
+def test_umma_probe_cta_pair(oracle, N, K):
+    """cta_group::2: one 256 x N x K GEMM over a cluster of two CTAs (layout of the fused kernel mlp_tc2.cu)."""
+    eng = make_engine(oracle, oracle.init_state_dict(0), "bf16")
+    g = torch.Generator().manual_seed(300 + N + K)
+    a = torch.randn(256, K, generator=g).bfloat16().float()
+    b = torch.randn(N, K, generator=g).bfloat16().float()
+    d = eng.umma_probe(3, a.cuda(), b.cuda())
+    torch.cuda.synchronize()
+    ref = a.double() @ b.double().T
+    assert maxabs(d, ref) <= 1e-3 * K ** 0.5, eng.watchdog()
+    eng.close()
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-5)])
 def test_mlp_forward_fp32_golden(oracle, precision, tol):
     g = load_golden("network_forward")
