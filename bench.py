@@ -317,7 +317,7 @@ def main():
     if mlp_launches > 0 and mlp_ms > 0:
         achieved = mlp_rows * FLOP_PER_EVAL / (mlp_ms / 1e3) / 1e12
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_sus, "unit": "TFLOP/s", "frac": achieved / peak_sus,
-                    "traffic": None, "kernel": "mlp_tc_forward_kernel", "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst),
+                    "traffic": None, "kernel": "mlp_tc_forward_kernel" if os.environ.get("NERF_TC_VARIANT") == "1" else "mlp_tc2_forward_kernel (CTA pair, tcgen05 cta_group::2)", "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst),
                     "launches_timed": mlp_launches, "avg_launch_ms": mlp_ms / mlp_launches,
                     "share_of_step": mlp_ms / total_ms,
                     "step_tflops": rays_per_step_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12}

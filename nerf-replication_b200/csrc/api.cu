@@ -3,10 +3,12 @@
 // fine MLP -> composite, each a kernel of this library launched on the caller's stream.
 #include <algorithm>
 #include <cstring>
+#include <cstdlib>
 #include "engine.h"
 
 namespace nerf {
 int tc_debug_read(unsigned int out[8]);
+int tc2_debug_read(unsigned int out[8]);
 }
 using namespace nerf;
 
@@ -44,6 +46,7 @@ extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) 
   h->cfg = *cfg;
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
+  if (const char* v = getenv("NERF_TC_VARIANT")) h->tc_variant = atoi(v) == 1 ? 1 : 2;
   *out = h;
   return NERF_OK;
 }
@@ -137,7 +140,7 @@ extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_
 static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep, cudaStream_t st) {
   if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_forward(h, net, src, raw, keep, st);
   if (h->profiling) cudaEventRecord(h->prof_event(), st);
-  const int rc = mlp_tc_forward(h, net, src, raw, st);
+  const int rc = h->tc_variant == 1 ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, st);
   if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; }
   return rc;
 }
@@ -463,4 +466,9 @@ extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* fla
 }
 
 // watchdog record of the tcgen05 kernels (valid after a trapped launch); out: 8 uint32
-extern "C" int nerf_debug_tc_watchdog(unsigned int* out8) { return nerf::tc_debug_read(out8); }
+extern "C" int nerf_debug_tc_watchdog(unsigned int* out8) {
+  unsigned int a[8], b[8];
+  const int r1 = nerf::tc_debug_read(a), r2 = nerf::tc2_debug_read(b);
+  for (int i = 0; i < 8; ++i) out8[i] = b[0] ? b[i] : a[i];
+  return r1 | r2;
+}

@@ -16,6 +16,7 @@ struct NerfEngine {
   __nv_bfloat16* wpack = nullptr;  // packed bf16 weight images for the tcgen05 kernels
   size_t wpack_bytes = 0;
   bool params_set = false;
+  int tc_variant = 2;              // 2 = CTA-pair kernel (mlp_tc2.cu), 1 = single-CTA kernel (mlp_tc.cu); env NERF_TC_VARIANT
 
   // grow-only named workspace buffers
   struct Buf { void* p = nullptr; size_t bytes = 0; };
@@ -117,6 +118,9 @@ int mlp_fp32_backward(NerfEngine* h, int net, const RowSrc& src, const float* d_
 size_t tc_wpack_bytes();
 void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
 int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
+
+// ---- mlp_tc2.cu (tcgen05 cta_group::2, CTA pairs; default) ----------------------------------------
+int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
 
 // ---- adam.cu -----------------------------------------------------------------------------------
 void launch_clip_adam(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr,

@@ -1,0 +1,381 @@
+// mlp_tc2.cu -- fused NeRF MLP forward on CTA pairs (tcgen05 cta_group::2), the default bf16 fast path.
+// Replaces Network.forward + batchify + NeRF.forward (network.py:49-74,163-171,199-258).
+//
+// Why pairs: with one CTA per SM (mlp_tc.cu) every SM streams the full 1.19 MB of layer weights per 256 rows,
+// the 64 KB weight ring leaves no shared memory for biases (they were fetched from L2 in the epilogue: the
+// critical path of round-1a, profiles/mlp_r1a_hot_sass.txt) and the B operand costs 64 B/clk of shared-memory
+// bandwidth.  A CTA pair issues M=256 MMAs: each CTA supplies its own 128 rows of A and HALF of the weight tile,
+// so per SM the weight traffic, the weight ring and the B-operand bandwidth are halved.
+//
+// Per CTA (cluster = 2 CTAs on one TPC, persistent over "pair super-tiles" of 512 rows; a CTA owns 256 of them
+// as two 128-row tiles X, Y that ping-pong between MMA and epilogue):
+//   warp 0      weight producer: this CTA's half of every stage image (16 KB: 128 weight rows x 64 k, bf16,
+//               128B-swizzled) via cp.async.bulk into a 3-deep ring, completion on mbarriers
+//   warp 1      rank 0: MMA issuer -- one lane issues tcgen05.mma.cta_group::2 (M=256, N=256|128, K=16) for X
+//               then Y on every stage; tcgen05.commit multicast to both CTAs' barriers
+//               rank 1: forwarder -- relays "my half of the stage has landed" to the leader's barrier
+//   warp 2      TMEM allocator (cta_group::2, 512 columns: X accumulators [0,256), Y [256,512))
+//   warps 4-7   tile X: positional encoding -> bf16 A operand; per layer TMEM -> +bias (shared memory), ReLU ->
+//               bf16 -> A operand of the next layer (in place); sigma / rgb heads on CUDA cores
+//   warps 8-11  same for tile Y
+// Shared memory (bytes): A_X 64K | A_Y 64K | PE_X 16K | PE_Y 16K | W ring 3 x 16K | biases 9.5K | heads 2.5K | barriers
+#include "engine.h"
+#include "tc_common.cuh"
+#include "rows.cuh"
+
+namespace nerf {
+using namespace tc;
+
+namespace v2 {
+
+constexpr int kTile = 128;
+constexpr int kRowsPerCta = 2 * kTile;          // X + Y
+constexpr int kRowsPerPair = 2 * kRowsPerCta;   // 512
+constexpr int kStageImage = 32768;              // packed stage image (both halves), see mlp_tc.cu pack_weights_kernel
+constexpr int kHalfBytes = 16384;               // this CTA's half of a 256-row stage (views layer: 8192)
+constexpr int kRing = 3;
+constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
+constexpr int kNumStages = 39;
+constexpr int kThreads = 384;
+constexpr int kBiasFloats = kNumSched * 256;    // bias of schedule entry li at [li*256, +N)
+constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
+constexpr uint32_t kOffBias = kOffW + kRing * kHalfBytes;         // 212992
+constexpr uint32_t kOffHeads = kOffBias + kBiasFloats * 4;        // 223232: w_alpha[256] | w_rgb[384]
+constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;         // 225792
+constexpr uint32_t kSmemBytes = kOffBar + 256;                    // 226048 <= 232448
+
+__host__ __device__ constexpr int sched_nkb(int li) { return li == 0 ? 1 : (li == 5 || li == 9) ? 5 : 4; }
+__host__ __device__ constexpr int sched_start(int li) {
+  int s = 0;
+  for (int i = 0; i < li; ++i) s += sched_nkb(i);
+  return s;
+}
+static_assert(sched_start(kNumSched) == kNumStages, "stage count");
+__host__ __device__ constexpr int sched_n(int li) { return li == 9 ? 128 : 256; }
+__host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li == 8 ? L_FEAT : L_VIEWS); }
+
+struct Bars {
+  uint64_t w_full[kRing], w_empty[kRing], acc_full[2], act_ready[2];
+  uint32_t tmem_slot;
+};
+
+__device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk, uint32_t a,
+                                            uint32_t b, uint32_t c, uint32_t d) {
+  *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
+}
+
+// packed fp32x2 add (FADD2 on sm_100): {a0,a1} += {b0,b1}
+__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb;\n\t"
+      "mov.b64 ra, {%0, %1};\n\t"
+      "mov.b64 rb, {%2, %3};\n\t"
+      "add.rn.f32x2 ra, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, ra;\n\t}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+
+// sin / cos of (x * 2^k) for the bf16 A operand: x * 2^k / (2 pi) is reduced to [-0.5, 0.5] turns with a two-term
+// constant (error ~1e-7 turns, far below bf16 resolution), then MUFU.SIN / MUFU.COS on [-pi, pi].
+// c_hi/c_lo = 2^k / (2 pi) split in two floats.
+__device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, float& s, float& c) {
+  const float r = x * c_hi;
+  const float k = rintf(r);
+  float fr = fmaf(x, c_hi, -k);
+  fr = fmaf(x, c_lo, fr);
+  const float ang = fr * 6.283185307179586f;
+  s = __sinf(ang);
+  c = __cosf(ang);
+}
+constexpr float kInv2PiHi = 0.15915493667125702f;          // fl(1/(2 pi))
+constexpr float kInv2PiLo = 6.4206382432985265e-09f;          // 1/(2 pi) - kInv2PiHi
+
+// Writes one 64-column bf16 K-block row: [v0 v1 v2 | sin(2^k v) cos(2^k v)]_{k<L} | zero pad, 8 columns per 16-byte chunk.
+template <int L>
+__device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, uint32_t row_xor, const float v[3]) {
+  float col[8];
+  int n = 0, chunk = 0;
+  auto push = [&](float x) {
+    col[n++] = x;
+    if (n == 8) {
+      store_chunk(blk, row_base, row_xor, chunk++, pack_bf16x2(col[0], col[1]), pack_bf16x2(col[2], col[3]),
+                  pack_bf16x2(col[4], col[5]), pack_bf16x2(col[6], col[7]));
+      n = 0;
+    }
+  };
+  push(v[0]); push(v[1]); push(v[2]);
+  float chi = kInv2PiHi, clo = kInv2PiLo;
+#pragma unroll
+  for (int k = 0; k < L; ++k, chi *= 2.0f, clo *= 2.0f) {
+    float sn[3], cs[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) sincos_turns(v[c], chi, clo, sn[c], cs[c]);
+    push(sn[0]); push(sn[1]); push(sn[2]); push(cs[0]); push(cs[1]); push(cs[2]);
+  }
+#pragma unroll
+  for (int z = 3 + 6 * L; z < 64; ++z) push(0.f);
+}
+
+// One 32-column chunk of a trunk-layer epilogue: acc + bias -> (ReLU) -> bf16 -> 4 x 16-byte chunks of the next
+// layer's A operand.  MODE 0: ReLU; 1: ReLU + sigma head accumulation on the fp32 values; 2: linear (feature).
+template <int MODE>
+__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const float* __restrict__ s_bias,
+                                          const float* __restrict__ s_walpha, float& sigma, uint8_t* sAct,
+                                          uint32_t row_base, uint32_t row_xor) {
+  uint32_t pk[16];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);     // warp-uniform address: broadcast
+    float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
+    float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
+    add2(f0, f1, bb.x, bb.y);
+    add2(f2, f3, bb.z, bb.w);
+    if (MODE == 2) {
+      pk[2 * j] = pack_bf16x2(f0, f1); pk[2 * j + 1] = pack_bf16x2(f2, f3);
+    } else {
+      if (MODE == 1) {
+        const float4 wa = *reinterpret_cast<const float4*>(s_walpha + c0 + 4 * j);
+        sigma = fmaf(fmaxf(f0, 0.f), wa.x, sigma); sigma = fmaf(fmaxf(f1, 0.f), wa.y, sigma);
+        sigma = fmaf(fmaxf(f2, 0.f), wa.z, sigma); sigma = fmaf(fmaxf(f3, 0.f), wa.w, sigma);
+      }
+      pk[2 * j] = pack_bf16x2_relu(f0, f1); pk[2 * j + 1] = pack_bf16x2_relu(f2, f3);
+    }
+  }
+  uint8_t* blk = sAct + (c0 >> 6) * 16384;
+  const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+}
+
+// Whole 256-column epilogue of one tile row, TMEM loads software-pipelined against the math of the previous chunk.
+template <int MODE>
+__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_walpha,
+                                          float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor) {
+  uint32_t va[32], vb[32];
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    tmem_wait_ld();
+    tmem_ld32(taddr + (c + 1) * 32, vb);
+    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor);
+    tmem_wait_ld();
+    if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
+    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor);
+  }
+}
+
+// View-branch epilogue: 128 columns, ReLU, then the 128 -> 3 rgb head on CUDA cores.
+__device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_wrgb,
+                                          float& r0, float& r1, float& r2) {
+  uint32_t va[32], vb[32];
+  auto chunk = [&](const uint32_t (&v)[32], int c0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);
+      float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
+      float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
+      add2(f0, f1, bb.x, bb.y);
+      add2(f2, f3, bb.z, bb.w);
+      const float hv[4] = {fmaxf(f0, 0.f), fmaxf(f1, 0.f), fmaxf(f2, 0.f), fmaxf(f3, 0.f)};
+      const float4 w0 = *reinterpret_cast<const float4*>(s_wrgb + c0 + 4 * j);
+      const float4 w1 = *reinterpret_cast<const float4*>(s_wrgb + 128 + c0 + 4 * j);
+      const float4 w2 = *reinterpret_cast<const float4*>(s_wrgb + 256 + c0 + 4 * j);
+      r0 = fmaf(hv[0], w0.x, r0); r0 = fmaf(hv[1], w0.y, r0); r0 = fmaf(hv[2], w0.z, r0); r0 = fmaf(hv[3], w0.w, r0);
+      r1 = fmaf(hv[0], w1.x, r1); r1 = fmaf(hv[1], w1.y, r1); r1 = fmaf(hv[2], w1.z, r1); r1 = fmaf(hv[3], w1.w, r1);
+      r2 = fmaf(hv[0], w2.x, r2); r2 = fmaf(hv[1], w2.y, r2); r2 = fmaf(hv[2], w2.z, r2); r2 = fmaf(hv[3], w2.w, r2);
+    }
+  };
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < 4; c += 2) {
+    tmem_wait_ld();
+    tmem_ld32(taddr + (c + 1) * 32, vb);
+    chunk(va, c * 32);
+    tmem_wait_ld();
+    if (c + 2 < 4) tmem_ld32(taddr + (c + 2) * 32, va);
+    chunk(vb, (c + 1) * 32);
+  }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
+                       const float* __restrict__ P, int64_t M, int64_t n_pair) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
+  float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
+  float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
+  float* s_wrgb = s_walpha + 256;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int64_t pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+
+  if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA12, smem_u32(smem));   // swizzle-128B needs 1024B alignment
+  if (tid == 0) {
+    for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
+    fence_barrier_init();
+  }
+  for (int li = 0; li < kNumSched; ++li)
+    for (int i = tid; i < sched_n(li); i += kThreads) s_bias[li * 256 + i] = __ldg(P + b_off(sched_layer(li)) + i);
+  for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(P + w_off(L_ALPHA) + i);
+  for (int i = tid; i < 384; i += kThreads) s_wrgb[i] = __ldg(P + w_off(L_RGB) + i);
+  cluster_sync_all();                      // barrier inits visible cluster-wide before any remote arrive / multicast commit
+  if (warp == 2) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sb.tmem_slot;
+
+  if (warp == 0) {
+    // ===== weight producer (both CTAs): my half of every stage =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t st = pair0; st < n_pair; st += pair_stride) {
+        for (int li = 0; li < kNumSched; ++li) {
+          const uint32_t bytes = (uint32_t)sched_n(li) * 64u;                 // half of the stage: N/2 rows x 128 B
+          for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
+            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+            mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
+            mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
+            bulk_g2s(smem + kOffW + slot * kHalfBytes,
+                     reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes,
+                     bytes, &sb.w_full[slot]);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1 && rank == 1) {
+    // ===== forwarder (peer CTA): relay local weight arrival to the leader's w_full =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t st = pair0; st < n_pair; st += pair_stride)
+        for (int s = 0; s < kNumStages; ++s, ++it) {
+          const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+          mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
+          mbar_arrive_cluster(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+        }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA) =====
+    if (lane == 0) {
+      uint32_t it = 0, lc = 0;
+      const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE), sW = smem_u32(smem + kOffW);
+      for (int64_t st = pair0; st < n_pair; st += pair_stride) {
+        for (int li = 0; li < kNumSched; ++li, ++lc) {
+          const int nkb = sched_nkb(li);
+          const uint32_t idesc = make_idesc_bf16(256, sched_n(li));
+          for (int kb = 0; kb < nkb; ++kb, ++it) {
+            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+            mbar_wait_cluster(&sb.w_full[slot], par, 0x20 + slot);
+            tc_fence_after();
+            int ablk;   // A source of this k-block: -1 = PE buffer, else hidden-activation block
+            if (li == 0) ablk = -1;
+            else if (li == 5) ablk = kb - 1;
+            else if (li == 9) ablk = kb < 4 ? kb : -1;
+            else ablk = kb;
+#pragma unroll
+            for (int tile = 0; tile < 2; ++tile) {
+              if (kb == 0) { mbar_wait_cluster(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+              const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
+              const uint32_t b_base = sW + slot * kHalfBytes;
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {
+                umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
+                         make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+              }
+              if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+            }
+            umma_commit2(&sb.w_empty[slot], 0x3);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===== PE + epilogue warps =====
+    const int tile = (warp - 4) >> 2, q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tile * 256u;
+    uint8_t* sAct = smem + kOffA + tile * 65536;
+    uint8_t* sPe = smem + kOffPE + tile * 16384;
+    const uint32_t row_base = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128), row_xor = (uint32_t)(row & 7);
+    const uint32_t ready_addr = mapa_u32(smem_u32(&sb.act_ready[tile]), 0);
+    auto signal_ready = [&]() {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(ready_addr);
+    };
+    uint32_t lc = 0;
+    for (int64_t st = pair0; st < n_pair; st += pair_stride) {
+      const int64_t g = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
+      const bool valid = g < M;
+      float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
+      if (valid) row_point(src, g, p, vd);
+      write_pe_block<10>(sPe, row_base, row_xor, p);
+      signal_ready();
+
+      float sigma = 0.f;
+      for (int li = 0; li < kNumSched; ++li, ++lc) {
+        mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
+        tc_fence_after();
+        const float* bias = s_bias + li * 256;
+        if (li < 9) {
+          if (li == 7) epi_layer<1>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
+          else if (li == 8) epi_layer<2>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
+          else epi_layer<0>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
+          // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
+          if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd);
+          signal_ready();
+        } else {
+          float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+          epi_views(taddr, bias, s_wrgb, r0, r1, r2);
+          tc_fence_before();
+          if (valid) {
+            float4 o = make_float4(r0 + __ldg(P + b_off(L_RGB)), r1 + __ldg(P + b_off(L_RGB) + 1), r2 + __ldg(P + b_off(L_RGB) + 2),
+                                   sigma + __ldg(P + b_off(L_ALPHA)));
+            if (src.mask && !src.mask[g]) o = make_float4(0.f, 0.f, 0.f, 0.f);
+            raw[g] = o;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc2(tmem, 512);
+}
+
+}  // namespace v2
+
+int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st) {
+  using namespace v2;
+  const int64_t M = src.R * src.S;
+  if (M <= 0) return NERF_OK;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_tc2_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2 smem attribute: ") + cudaGetErrorString(e));
+    attr_set = true;
+  }
+  const int64_t n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
+  const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
+  const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
+  const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
+  mlp_tc2_forward_kernel<<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair);
+  h->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));
+  return NERF_OK;
+}
+
+int tc2_debug_read(unsigned int out[8]) {
+  unsigned int tmp[8];
+  cudaError_t e = cudaMemcpyFromSymbol(tmp, g_tc_debug, sizeof(tmp));
+  for (int i = 0; i < 8; ++i) out[i] = tmp[i];
+  return e == cudaSuccess ? 0 : -1;
+}
+
+}  // namespace nerf
