@@ -253,7 +253,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
         for (int s = 0; s < kNumStages; ++s, ++it) {
           const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
           mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
-          mbar_arrive_cluster(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+          mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
         }
     }
     __syncwarp();
@@ -268,7 +268,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           const uint32_t idesc = make_idesc_bf16(256, sched_n(li));
           for (int kb = 0; kb < nkb; ++kb, ++it) {
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-            mbar_wait_cluster(&sb.w_full[slot], par, 0x20 + slot);
+            mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
             tc_fence_after();
             int ablk;   // A source of this k-block: -1 = PE buffer, else hidden-activation block
             if (li == 0) ablk = -1;
@@ -277,7 +277,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
             else ablk = kb;
 #pragma unroll
             for (int tile = 0; tile < 2; ++tile) {
-              if (kb == 0) { mbar_wait_cluster(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+              if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
               const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
               const uint32_t b_base = sW + slot * kHalfBytes;
 #pragma unroll
@@ -306,7 +306,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(ready_addr);
+      if (lane == 0) mbar_arrive_remote(ready_addr);
     };
     uint32_t lc = 0;
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {

@@ -193,6 +193,12 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// same, default semantics (release at CTA scope): what CUTLASS's ClusterBarrier::arrive(cta_id) emits.  The
+// .release.cluster form above costs MEMBAR.ALL.GPU + ERRBAR per arrive (profiles/mlp_r1b_hot_sass.txt); the
+// CTA-scope form is enough when the data guarded is this CTA's own shared memory read by this SM's tensor core.
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
