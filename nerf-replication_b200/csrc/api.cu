@@ -140,7 +140,7 @@ extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_
 static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep, cudaStream_t st) {
   if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_forward(h, net, src, raw, keep, st);
   if (h->profiling) cudaEventRecord(h->prof_event(), st);
-  const int rc = h->tc_variant == 1 ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, st);
+  const int rc = h->tc_variant == 1 ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, nullptr, st);
   if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; }
   return rc;
 }

@@ -120,7 +120,7 @@ void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cud
 int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
 
 // ---- mlp_tc2.cu (tcgen05 cta_group::2, CTA pairs; default) ----------------------------------------
-int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
+int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8_t* act_arena, cudaStream_t st);
 
 // ---- adam.cu -----------------------------------------------------------------------------------
 void launch_clip_adam(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr,

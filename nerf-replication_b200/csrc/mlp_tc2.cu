@@ -22,6 +22,7 @@
 #include "engine.h"
 #include "tc_common.cuh"
 #include "rows.cuh"
+#include "tc_arena.cuh"
 
 namespace nerf {
 using namespace tc;
@@ -113,7 +114,8 @@ __device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, 
     push(sn[0]); push(sn[1]); push(sn[2]); push(cs[0]); push(cs[1]); push(cs[2]);
   }
 #pragma unroll
-  for (int z = 3 + 6 * L; z < 64; ++z) push(0.f);
+  for (int z = 3 + 6 * L; z < 63; ++z) push(0.f);
+  push(1.0f);     // column 63 = 1: its weight column is zero in the forward; in wgrad it yields the bias gradient
 }
 
 // One 32-column chunk of a trunk-layer epilogue: acc + bias -> (ReLU) -> bf16 -> 4 x 16-byte chunks of the next
@@ -165,10 +167,12 @@ __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restric
 }
 
 // View-branch epilogue: 128 columns, ReLU, then the 128 -> 3 rgb head on CUDA cores.
+template <bool SAVE>
 __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_wrgb,
-                                          float& r0, float& r1, float& r2) {
+                                          float& r0, float& r1, float& r2, uint8_t* sAct, uint32_t row_base, uint32_t row_xor) {
   uint32_t va[32], vb[32];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
+    uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);
@@ -176,6 +180,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
       add2(f0, f1, bb.x, bb.y);
       add2(f2, f3, bb.z, bb.w);
+      if (SAVE) { pk[2 * j] = pack_bf16x2_relu(f0, f1); pk[2 * j + 1] = pack_bf16x2_relu(f2, f3); }
       const float hv[4] = {fmaxf(f0, 0.f), fmaxf(f1, 0.f), fmaxf(f2, 0.f), fmaxf(f3, 0.f)};
       const float4 w0 = *reinterpret_cast<const float4*>(s_wrgb + c0 + 4 * j);
       const float4 w1 = *reinterpret_cast<const float4*>(s_wrgb + 128 + c0 + 4 * j);
@@ -183,6 +188,12 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       r0 = fmaf(hv[0], w0.x, r0); r0 = fmaf(hv[1], w0.y, r0); r0 = fmaf(hv[2], w0.z, r0); r0 = fmaf(hv[3], w0.w, r0);
       r1 = fmaf(hv[0], w1.x, r1); r1 = fmaf(hv[1], w1.y, r1); r1 = fmaf(hv[2], w1.z, r1); r1 = fmaf(hv[3], w1.w, r1);
       r2 = fmaf(hv[0], w2.x, r2); r2 = fmaf(hv[1], w2.y, r2); r2 = fmaf(hv[2], w2.z, r2); r2 = fmaf(hv[3], w2.w, r2);
+    }
+    if (SAVE) {   // keep the hidden view activations (bf16 image in A blocks 0,1) for the backward pass
+      uint8_t* blk = sAct + (c0 >> 6) * 16384;
+      const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
     }
   };
   tmem_ld32(taddr, va);
@@ -197,9 +208,12 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
   }
 }
 
+// SAVE: training forward -- every A-operand block (PE, h_0..h_7, feature, PE(dir), view hidden) is also bulk-stored
+// (TMA engine, shared -> global) to the activation arena as it is produced (tc_arena.cuh).
+template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
-                       const float* __restrict__ P, int64_t M, int64_t n_pair) {
+                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
@@ -308,19 +322,40 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
+    // SAVE: the tile's first lane issues the bulk stores; before any in-place overwrite of a stored block it waits
+    // until the TMA engine has finished reading shared memory, then releases the other 127 threads of the tile.
+    const bool tile_leader = (q == 0 && lane == 0);
+    const uint32_t bar_id = 1 + tile;
+    auto before_overwrite = [&]() {
+      if (SAVE) { if (tile_leader) bulk_wait_read0(); named_bar_sync(bar_id, kTile); }
+    };
+    auto save_blocks = [&](uint8_t* tile_base, int slot, const uint8_t* smem_src, int nblocks) {
+      if (SAVE) {
+        named_bar_sync(bar_id, kTile);          // every thread's rows are written and proxy-fenced (signal_ready)
+        if (tile_leader) {
+          for (int b = 0; b < nblocks; ++b)
+            bulk_s2g(tile_base + (size_t)(slot + b) * arena::kBlockBytes, smem_src + b * 16384, arena::kBlockBytes);
+          bulk_commit();
+        }
+      }
+    };
     uint32_t lc = 0;
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {
       const int64_t g = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
       const bool valid = g < M;
+      uint8_t* tile_base = SAVE ? act_arena + (size_t)(((st * 2 + rank) * 2 + tile)) * arena::act_tile_bytes() : nullptr;
       float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
       if (valid) row_point(src, g, p, vd);
+      before_overwrite();
       write_pe_block<10>(sPe, row_base, row_xor, p);
       signal_ready();
+      save_blocks(tile_base, arena::kActPE, sPe, 1);
 
       float sigma = 0.f;
       for (int li = 0; li < kNumSched; ++li, ++lc) {
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
+        before_overwrite();
         const float* bias = s_bias + li * 256;
         if (li < 9) {
           if (li == 7) epi_layer<1>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
@@ -329,10 +364,13 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
           if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd);
           signal_ready();
+          save_blocks(tile_base, li < 8 ? arena::kActH + 4 * li : arena::kActFeat, sAct, 4);
+          if (SAVE && li == 5 && tile_leader) { bulk_s2g(tile_base + (size_t)arena::kActPEDir * arena::kBlockBytes, sPe, arena::kBlockBytes); bulk_commit(); }
         } else {
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-          epi_views(taddr, bias, s_wrgb, r0, r1, r2);
+          epi_views<SAVE>(taddr, bias, s_wrgb, r0, r1, r2, sAct, row_base, row_xor);
           tc_fence_before();
+          if (SAVE) { fence_proxy_async_smem(); save_blocks(tile_base, arena::kActHV, sAct, 2); }
           if (valid) {
             float4 o = make_float4(r0 + __ldg(P + b_off(L_RGB)), r1 + __ldg(P + b_off(L_RGB) + 1), r2 + __ldg(P + b_off(L_RGB) + 2),
                                    sigma + __ldg(P + b_off(L_ALPHA)));
@@ -342,6 +380,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
         }
       }
     }
+    if (SAVE && tile_leader) bulk_wait0();       // outstanding bulk stores must complete before the CTA may exit
   }
   tc_fence_before();
   cluster_sync_all();
@@ -350,13 +389,15 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
 
 }  // namespace v2
 
-int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st) {
+// act_arena != NULL: training forward, activations saved as tile images (needs arena::num_tiles(M) * act_tile_bytes()).
+int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8_t* act_arena, cudaStream_t st) {
   using namespace v2;
   const int64_t M = src.R * src.S;
   if (M <= 0) return NERF_OK;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_tc2_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(mlp_tc2_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_tc2_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2 smem attribute: ") + cudaGetErrorString(e));
     attr_set = true;
   }
@@ -364,7 +405,8 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaS
   const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
-  mlp_tc2_forward_kernel<<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair);
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));

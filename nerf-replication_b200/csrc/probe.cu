@@ -161,10 +161,74 @@ umma_probe2_kernel(const float* __restrict__ A, const float* __restrict__ B, flo
   if (warp == 0) tmem_dealloc2(tmem, 512);
 }
 
+// variant 4: both operands MN-major (the wgrad form): D[128 x N] = At^T * Bt with At [K x 128], Bt [K x N]
+// (K = reduction dim = "rows").  The operands are staged as [rows x 64-column] 128B-swizzled blocks -- the very
+// images the forward saves -- and described as MN-major: LBO = distance between 64-column blocks, SBO = 1024
+// (8-row groups), one K=16 step = 16 rows = +2048 bytes.
+__global__ void __launch_bounds__(128, 1)
+umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt, float* __restrict__ D, int N, int K) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar_done;
+  __shared__ uint32_t tmem_base_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint8_t* sA = smem;                 // 2 blocks x 16 KB
+  uint8_t* sB = smem + 2 * 16384;     // N/64 blocks x 16 KB
+  if (warp == 0) { tmem_alloc(&tmem_base_slot, 512); tmem_relinquish(); }
+  if (tid == 32) { mbar_init(&bar_done, 1); fence_barrier_init(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_slot;
+  for (int e = tid; e < K * 128; e += 128) {
+    const int r = e / 128, c = e % 128;
+    *reinterpret_cast<__nv_bfloat16*>(sA + (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2) = __float2bfloat16(At[e]);
+  }
+  for (int e = tid; e < K * N; e += 128) {
+    const int r = e / N, c = e % N;
+    *reinterpret_cast<__nv_bfloat16*>(sB + (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2) = __float2bfloat16(Bt[e]);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (tid == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, N, 1, 1);
+    for (int ks = 0; ks < K / 16; ++ks) {
+      const uint64_t ad = make_smem_desc(smem_u32(sA) + ks * 2048, 16384, 1024, kLayoutSW128);
+      const uint64_t bd = make_smem_desc(smem_u32(sB) + ks * 2048, 16384, 1024, kLayoutSW128);
+      umma_ss(tmem, ad, bd, idesc, ks > 0);
+    }
+    umma_commit(&bar_done);
+  }
+  mbar_wait(&bar_done, 0, 0x104);
+  tc_fence_after();
+  {
+    const int row = warp * 32 + lane;
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) D[row * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 }  // namespace nerf
 
 extern "C" int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K, void* stream) {
   using namespace nerf;
+  if (variant == 4) {   // a = At [K x 128], b = Bt [K x N]
+    if (M != 128 || N % 64 || N < 64 || N > 256 || K % 16 || K < 16 || K > 128) return NERF_E_INVALID;
+    const size_t smem4 = (size_t)(2 + N / 64) * 16384 + 1024;
+    if (cudaFuncSetAttribute(umma_probe_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4) != cudaSuccess) return NERF_E_CUDA;
+    umma_probe_mn_kernel<<<1, 128, smem4, (cudaStream_t)stream>>>(a, b, d, N, K);
+    return cudaGetLastError() == cudaSuccess ? NERF_OK : NERF_E_CUDA;
+  }
   if (variant == 3) {
     if (M != 256 || N % 32 || N < 32 || N > 256 || K % 64 || K < 64 || K > 256) return NERF_E_INVALID;
     const size_t smem2 = (size_t)(K / 64) * 16384 + (size_t)K * (N / 2) * 2 + 1024;

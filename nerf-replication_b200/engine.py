@@ -243,8 +243,12 @@ class Engine:
 
     # -- debug ----------------------------------------------------------------------------------
     def umma_probe(self, variant, a, b):
-        M, K = a.shape
-        N = b.shape[0]
+        if variant == 4:                       # MN-major operands: a = At [K, 128], b = Bt [K, N]
+            K, M = a.shape
+            N = b.shape[1]
+        else:
+            M, K = a.shape
+            N = b.shape[0]
         d = torch.zeros(M, N, device=a.device)
         rc = self.lib.nerf_debug_umma_probe(variant, self._p(a, name="a"), self._p(b, name="b"), d.data_ptr(), M, N, K, self._stream())
         if rc != 0:

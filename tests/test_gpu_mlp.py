@@ -39,6 +39,20 @@ def test_umma_probe_cta_pair(oracle, N, K):
     eng.close()
 
 
+@pytest.mark.parametrize("N,K", [(256, 128), (64, 128), (128, 64), (192, 16)])
+def test_umma_probe_mn_major(oracle, N, K):
+    """Both operands MN-major (wgrad form): D[128 x N] = At^T Bt, reduction over K rows of saved tile images."""
+    eng = make_engine(oracle, oracle.init_state_dict(0), "bf16")
+    g = torch.Generator().manual_seed(400 + N + K)
+    at = torch.randn(K, 128, generator=g).bfloat16().float()
+    bt = torch.randn(K, N, generator=g).bfloat16().float()
+    d = eng.umma_probe(4, at.cuda(), bt.cuda())
+    torch.cuda.synchronize()
+    ref = at.double().T @ bt.double()
+    assert maxabs(d, ref) <= 1e-3 * K ** 0.5, eng.watchdog()
+    eng.close()
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-5)])
 def test_mlp_forward_fp32_golden(oracle, precision, tol):
     g = load_golden("network_forward")
