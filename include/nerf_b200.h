@@ -153,7 +153,8 @@ int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d,
                           void* stream);
 
 /* watchdog record of the tcgen05 kernels: a barrier that never completes traps the kernel instead of
- * hanging the GPU and leaves {tag, blockIdx, threadIdx, parity, ...} here.  out8: 8 uint32 (host). */
+ * hanging the GPU and leaves {tag, blockIdx, threadIdx, parity, ...} here.  out8: 64 uint32 (host): [0,8) first record,
+ * [8,64) one word per stuck waiter (tag | warp << 12 | block << 16 | parity << 31). */
 int nerf_debug_tc_watchdog(unsigned int* out8);
 
 #ifdef __cplusplus

@@ -5,14 +5,20 @@
 #include <cstring>
 #include <cstdlib>
 #include "engine.h"
+#include "tc_arena.cuh"
 
 namespace nerf {
 int tc_debug_read(unsigned int out[8]);
 int tc2_debug_read(unsigned int out[8]);
+void tc1_set_debug_sink(unsigned int*);
+void tc2_set_debug_sink(unsigned int*);
+void tc2b_set_debug_sink(unsigned int*);
+void tcp_set_debug_sink(unsigned int*);
 }
 using namespace nerf;
 
 static std::string g_create_error;
+static unsigned int* g_watchdog_host = nullptr;   // host-mapped, survives a trapped kernel
 
 static int check_cfg(const NerfConfig& c, std::string* why) {
   if (c.n_samples < 4 || c.n_samples > 1024) { *why = "n_samples must be in [4,1024]"; return NERF_E_INVALID; }
@@ -42,6 +48,18 @@ extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) 
     return NERF_E_INVALID;
   }
   cudaSetDevice(device);
+  if (!g_watchdog_host) {
+    unsigned int* hp = nullptr;
+    if (cudaHostAlloc(&hp, 256, cudaHostAllocMapped) == cudaSuccess) {
+      memset(hp, 0, 256);
+      unsigned int* dp = nullptr;
+      if (cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess) {
+        g_watchdog_host = hp;
+        tc1_set_debug_sink(dp); tc2_set_debug_sink(dp); tc2b_set_debug_sink(dp); tcp_set_debug_sink(dp);
+      }
+    }
+    cudaGetLastError();
+  }
   NerfEngine* h = new NerfEngine();
   h->cfg = *cfg;
   h->device = device;
@@ -57,6 +75,7 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   cudaDeviceSynchronize();
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
   if (h->wpack) cudaFree(h->wpack);
+  if (h->wpack_bwd) cudaFree(h->wpack_bwd);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   for (int i = 0; i < 2; ++i) {
     if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
@@ -95,7 +114,9 @@ extern "C" int nerf_set_params(NerfEngine* h, const float* flat, void* stream) {
     NERF_CUDA_TRY(h, cudaMalloc(&h->wpack, h->wpack_bytes));
     NERF_CUDA_TRY(h, cudaMemsetAsync(h->wpack, 0, h->wpack_bytes, (cudaStream_t)stream));
   }
+  if (!h->wpack_bwd) NERF_CUDA_TRY(h, cudaMalloc(&h->wpack_bwd, tc_bwd_wpack_bytes()));
   tc_pack_weights(h, flat, h->wpack, (cudaStream_t)stream);
+  tc_pack_dgrad_weights(h, flat, h->wpack_bwd, (cudaStream_t)stream);
   h->params_set = true;
   return post(h, "nerf_set_params");
 }
@@ -137,10 +158,17 @@ extern "C" int nerf_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_
   return post(h, "nerf_freq_encode");
 }
 
+static const char* act_arena_name(int net) { return net == NERF_NET_FINE ? "tc.act_f" : "tc.act_c"; }
+
 static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool keep, cudaStream_t st) {
   if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_forward(h, net, src, raw, keep, st);
+  uint8_t* act = nullptr;
+  if (keep) {   // training forward: activations saved as tile images for the tensor-core backward
+    int rc0 = h->buf(act_arena_name(net), (size_t)arena::num_tiles(src.R * src.S) * arena::act_tile_bytes(), &act);
+    if (rc0) return rc0;
+  }
   if (h->profiling) cudaEventRecord(h->prof_event(), st);
-  const int rc = h->tc_variant == 1 ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, nullptr, st);
+  const int rc = (h->tc_variant == 1 && !keep) ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, act, st);
   if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; }
   return rc;
 }
@@ -370,8 +398,6 @@ extern "C" int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, co
 // through PE -> t_fine -> inverse CDF -> coarse weights -> coarse sigma -> coarse trunk.
 static int train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
                          const float* u, float* rgb, float* depth, cudaStream_t st) {
-  if (h->cfg.precision != NERF_PRECISION_FP32)
-    return h->fail(NERF_E_INVALID, "training: the backward pass exists in NERF_PRECISION_FP32 mode only in this build");
   NerfRenderOut out{};
   out.rgb = rgb; out.depth = depth;
   RenderTaps tp;
@@ -380,6 +406,25 @@ static int train_forward(NerfEngine* h, const float* rays_o, const float* rays_d
   h->taps.t_c = tp.t_c; h->taps.raw_c = tp.raw_c; h->taps.t_s = tp.t_s; h->taps.raw_f = tp.raw_f;
   h->taps.sort_idx = tp.sort_idx; h->taps.call_id = tp.call_id; h->taps.n = n; h->taps.jitter = jitter; h->taps.u = u;
   return NERF_OK;
+}
+
+// MLP backward of one net: fp32 validation kernels, or the tensor-core dgrad chain + wgrad over the saved tile images.
+static int mlp_backward(NerfEngine* h, int net, const RowSrc& src, const float* d_raw, bool sigma_only, float* G, float* d_t,
+                        cudaStream_t st) {
+  if (h->cfg.precision == NERF_PRECISION_FP32) return mlp_fp32_backward(h, net, src, d_raw, sigma_only, G, d_t, st);
+  const int64_t M = src.R * src.S;
+  const bool full = !sigma_only;
+  uint8_t *act, *grad;
+  float* scratch = nullptr;
+  int rc;
+  if ((rc = h->buf(act_arena_name(net), (size_t)arena::num_tiles(M) * arena::act_tile_bytes(), &act))) return rc;
+  if ((rc = h->buf("tc.grad", (size_t)arena::num_tiles(M) * arena::grad_tile_bytes(), &grad))) return rc;
+  if (full && (rc = h->buf("tc.pe_scratch", (size_t)M * 64, &scratch))) return rc;
+  if (full && !d_t) {   // coarse-only rendering: the input gradient is not needed; give the kernel a sink
+    if ((rc = h->buf("tc.dt_sink", (size_t)M, &d_t))) return rc;
+  }
+  if ((rc = mlp_tc2_dgrad(h, net, full, src, d_raw, act, grad, scratch, d_t, st))) return rc;
+  return mlp_tc2_wgrad(h, full, M, d_raw, act, grad, G, st);
 }
 
 static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
@@ -399,19 +444,19 @@ static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_
     if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
     launch_composite_bwd(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_f, d_t_s, st);
     src.t = tp.t_s; src.S = Nt;
-    if ((rc = mlp_fp32_backward(h, NERF_NET_FINE, src, d_raw_f, false, flat_grad + NERF_PARAMS_PER_NET, d_t_s, st))) return rc;
+    if ((rc = mlp_backward(h, NERF_NET_FINE, src, d_raw_f, false, flat_grad + NERF_PARAMS_PER_NET, d_t_s, st))) return rc;
     const bool tu = c.train_u != 0;
     if ((rc = launch_sample_pdf_bwd(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? tp.u : nullptr, tu && !tp.u, tp.call_id, d_t_s,
                                     tp.sort_idx, d_w_c, st))) return rc;
     launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, nullptr, nullptr, d_w_c, d_raw_c, nullptr, st);
     src.t = tp.t_c; src.S = Nc;
-    if ((rc = mlp_fp32_backward(h, NERF_NET_COARSE, src, d_raw_c, true, flat_grad, nullptr, st))) return rc;
+    if ((rc = mlp_backward(h, NERF_NET_COARSE, src, d_raw_c, true, flat_grad, nullptr, st))) return rc;
   } else {
     float* d_raw_c;
     if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
     launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_c, nullptr, st);
     src.t = tp.t_c; src.S = Nc;
-    if ((rc = mlp_fp32_backward(h, NERF_NET_COARSE, src, d_raw_c, false, flat_grad, nullptr, st))) return rc;
+    if ((rc = mlp_backward(h, NERF_NET_COARSE, src, d_raw_c, false, flat_grad, nullptr, st))) return rc;
   }
   return post(h, "train_backward");
 }
@@ -461,12 +506,16 @@ extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* fla
     return h->fail(NERF_E_INVALID, "nerf_clip_adam: buffers must be 16-byte aligned");
   cudaSetDevice(h->device);
   launch_clip_adam(h, flat_param, flat_grad, m, v, NERF_PARAMS_TOTAL, lr, beta1, beta2, eps, clip, step, (cudaStream_t)stream);
-  if (h->params_set && flat_param == h->params && h->wpack) tc_pack_weights(h, flat_param, h->wpack, (cudaStream_t)stream);
+  if (h->params_set && flat_param == h->params && h->wpack) {
+    tc_pack_weights(h, flat_param, h->wpack, (cudaStream_t)stream);
+    tc_pack_dgrad_weights(h, flat_param, h->wpack_bwd, (cudaStream_t)stream);
+  }
   return post(h, "nerf_clip_adam");
 }
 
 // watchdog record of the tcgen05 kernels (valid after a trapped launch); out: 8 uint32
 extern "C" int nerf_debug_tc_watchdog(unsigned int* out8) {
+  if (g_watchdog_host && g_watchdog_host[0]) { for (int i = 0; i < 64; ++i) out8[i] = g_watchdog_host[i]; return 0; }
   unsigned int a[8], b[8];
   const int r1 = nerf::tc_debug_read(a), r2 = nerf::tc2_debug_read(b);
   for (int i = 0; i < 8; ++i) out8[i] = b[0] ? b[i] : a[i];

@@ -15,6 +15,7 @@ struct NerfEngine {
   const float* params = nullptr;   // caller-owned fp32 masters (flat layout)
   __nv_bfloat16* wpack = nullptr;  // packed bf16 weight images for the tcgen05 kernels
   size_t wpack_bytes = 0;
+  __nv_bfloat16* wpack_bwd = nullptr;   // transposed stage images for the dgrad chain (mlp_tc2_bwd.cu)
   bool params_set = false;
   int tc_variant = 2;              // 2 = CTA-pair kernel (mlp_tc2.cu), 1 = single-CTA kernel (mlp_tc.cu); env NERF_TC_VARIANT
 
@@ -121,6 +122,15 @@ int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaSt
 
 // ---- mlp_tc2.cu (tcgen05 cta_group::2, CTA pairs; default) ----------------------------------------
 int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8_t* act_arena, cudaStream_t st);
+
+// ---- mlp_tc2_bwd.cu (tensor-core backward) -----------------------------------------------------------
+size_t tc_bwd_wpack_bytes();
+void tc_pack_dgrad_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
+int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const float* d_raw, const uint8_t* act_arena,
+                  uint8_t* grad_arena, float* pe_scratch, float* d_t, cudaStream_t st);
+
+int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const uint8_t* act_arena, const uint8_t* grad_arena,
+                  float* flat_grad_net, cudaStream_t st);
 
 // ---- adam.cu -----------------------------------------------------------------------------------
 void launch_clip_adam(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr,

@@ -331,4 +331,6 @@ int tc_debug_read(unsigned int out[8]) {
   return e == cudaSuccess ? 0 : -1;
 }
 
+NERF_TC_DEFINE_DEBUG_SINK(tc1_set_debug_sink)
+
 }  // namespace nerf

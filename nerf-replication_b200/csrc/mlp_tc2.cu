@@ -420,4 +420,6 @@ int tc2_debug_read(unsigned int out[8]) {
   return e == cudaSuccess ? 0 : -1;
 }
 
+NERF_TC_DEFINE_DEBUG_SINK(tc2_set_debug_sink)
+
 }  // namespace nerf

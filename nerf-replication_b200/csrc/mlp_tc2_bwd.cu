@@ -1,0 +1,757 @@
+// mlp_tc2_bwd.cu -- tensor-core backward of the NeRF MLP (bf16 operands, fp32 accumulate), two kernels:
+//
+//   dgrad chain  (this file, part 1): per 128-row tile the whole chain  d raw -> d hv -> d feature -> dZ7 ... dZ0
+//                (-> d PE -> d t for the fine net) runs inside one persistent CTA-pair kernel; the gradient tile
+//                stays in shared memory as the A operand of the next tcgen05.mma (M=256, cta_group::2), transposed
+//                weight stage images stream through a 3-deep ring, the ReLU masks come from the activation images
+//                the forward saved (streamed through a second ring), and every dZ_l tile is bulk-stored to the
+//                gradient arena for the weight-gradient kernel.
+//   wgrad        (part 2): dW_l = dZ_l^T X_{l-1} summed over all rows -- the saved tile images are used directly as
+//                MN-major operands (reduction dimension = rows), accumulators [256 x 384] fp32 in TMEM across a CTA
+//                pair, one red.global.add flush per (layer, tile range) work unit.
+//
+// Reference graph: autograd of network.py:49-74 as exercised by trainers/nerf.py:27-33: the fine
+// net needs all weight gradients and the input gradient down to t; the coarse net only receives d sigma.
+#include "engine.h"
+#include "tc_common.cuh"
+#include "rows.cuh"
+#include "tc_arena.cuh"
+
+namespace nerf {
+using namespace tc;
+
+namespace bw {
+
+constexpr int kTile = 128;
+constexpr int kRowsPerCta = 256, kRowsPerPair = 512;
+constexpr int kStageImage = 32768;
+constexpr int kHalfBytes = 16384;
+constexpr int kRing = 2;        // weight stages in flight
+constexpr int kMaskRing = 2;    // mask blocks in flight PER TILE (each tile has its own ring and producer lane: a shared ring
+                                // lets the later tile wait more than one ring cycle ahead, where parity waits alias)
+constexpr int kThreads = 384;
+constexpr int kNumSteps = 11;      // V1, F, L7, L6, PE5, L5, L4, L3, L2, L1, P0
+constexpr int kNumStages = 42;
+enum Step { S_V1 = 0, S_F = 1, S_L7 = 2, S_L6 = 3, S_PE5 = 4, S_L5 = 5, S_L4 = 6, S_L3 = 7, S_L2 = 8, S_L1 = 9, S_P0 = 10 };
+
+__host__ __device__ constexpr int step_nkb(int s) { return s == S_V1 ? 2 : 4; }
+__host__ __device__ constexpr int step_n(int s) { return (s == S_PE5 || s == S_P0) ? 64 : 256; }
+__host__ __device__ constexpr int step_stage0(int s) {
+  int a = 0;
+  for (int i = 0; i < s; ++i) a += step_nkb(i);
+  return a;
+}
+static_assert(step_stage0(kNumSteps) == kNumStages, "dgrad stage count");
+// reference layer whose weight the step multiplies by, and the first input column of that weight it produces
+__host__ __device__ constexpr int step_layer(int s) {
+  return s == S_V1 ? L_VIEWS : s == S_F ? L_FEAT : s == S_L7 ? 7 : s == S_L6 ? 6 : (s == S_PE5 || s == S_L5) ? 5
+       : s == S_L4 ? 4 : s == S_L3 ? 3 : s == S_L2 ? 2 : s == S_L1 ? 1 : 0;
+}
+__host__ __device__ constexpr int step_col0(int s) { return s == S_L5 ? 63 : 0; }
+__host__ __device__ constexpr int step_ncols(int s) { return (s == S_PE5 || s == S_P0) ? 63 : 256; }
+// activation-arena slot of the ReLU mask the step's epilogue applies (-1: none) and gradient-arena slot it writes
+__host__ __device__ constexpr int step_mask_slot(int s) {
+  return s == S_F ? arena::kActH + 28 : s == S_L7 ? arena::kActH + 24 : s == S_L6 ? arena::kActH + 20
+       : s == S_L5 ? arena::kActH + 16 : s == S_L4 ? arena::kActH + 12 : s == S_L3 ? arena::kActH + 8
+       : s == S_L2 ? arena::kActH + 4 : s == S_L1 ? arena::kActH + 0 : -1;
+}
+__host__ __device__ constexpr int step_out_slot(int s) {
+  return s == S_V1 ? arena::kGradFeat : s == S_F ? arena::kGradZ + 28 : s == S_L7 ? arena::kGradZ + 24
+       : s == S_L6 ? arena::kGradZ + 20 : s == S_L5 ? arena::kGradZ + 16 : s == S_L4 ? arena::kGradZ + 12
+       : s == S_L3 ? arena::kGradZ + 8 : s == S_L2 ? arena::kGradZ + 4 : s == S_L1 ? arena::kGradZ + 0 : -1;
+}
+
+// shared memory map
+constexpr uint32_t kOffA = 0, kOffW = 131072, kOffMask = kOffW + kRing * kHalfBytes;      // 180224
+constexpr uint32_t kOffHeads = kOffMask + 2 * kMaskRing * 16384;                                // 229376: w_alpha[256] | w_rgb[384]
+constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;                                   // 231936
+constexpr uint32_t kSmemBytes = kOffBar + 256;                                              // 232192 <= 232448
+
+struct Bars {
+  uint64_t w_full[kRing], w_empty[kRing], m_full[2][kMaskRing], m_empty[2][kMaskRing], acc_full[2], act_ready[2];
+  uint32_t tmem_slot;
+};
+static_assert(sizeof(Bars) <= 256, "barrier block");
+
+}  // namespace bw
+
+size_t tc_bwd_wpack_bytes() { return (size_t)2 * bw::kNumStages * bw::kStageImage; }
+
+// Transposed weight stage images for the dgrad chain: stage (step s, k-block kb) = B[n][k] = W_layer[kb*64 + k][col0 + n]
+// for n < ncols (zero beyond), [N rows x 64 k] bf16, K-major, 128B swizzle.
+__global__ void pack_dgrad_weights_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack) {
+  using namespace bw;
+  const int64_t total = (int64_t)2 * kNumStages * 256 * 64;
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(e & 63), n = (int)((e >> 6) & 255);
+    const int stg = (int)((e >> 14) % kNumStages), net = (int)((e >> 14) / kNumStages);
+    int s = 0;
+    while (s + 1 < kNumSteps && step_stage0(s + 1) <= stg) ++s;
+    const int kb = stg - step_stage0(s);
+    if (n >= step_n(s)) continue;
+    const int layer = step_layer(s);
+    const LayerDim d = layer_dim(layer);
+    const int out = kb * 64 + k;                     // output feature of the layer = reduction index of dgrad
+    float w = 0.f;
+    if (n < step_ncols(s) && out < d.out) w = flat[(int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + (int64_t)out * d.in + step_col0(s) + n];
+    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + stg) * kStageImage + sw128_offset(n, k >> 3) + (k & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16(w);
+  }
+}
+
+void tc_pack_dgrad_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st) {
+  pack_dgrad_weights_kernel<<<h->num_sms * 8, 256, 0, st>>>(flat, wpack);
+  h->launches++;
+}
+
+namespace bw {
+
+__device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk, uint32_t a,
+                                            uint32_t b, uint32_t c, uint32_t d) {
+  *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
+}
+__device__ __forceinline__ uint4 load_chunk(const uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk) {
+  return *reinterpret_cast<const uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4));
+}
+// per-half "h > 0" mask of a post-ReLU bf16x2 word: 0xFFFF where the half is positive (HSET2.BF16)
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t h) {
+  uint32_t d, z = 0;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(z));
+  return d;
+}
+
+constexpr float kInv2PiHi = 0.15915493667125702f, kInv2PiLo = 6.4206382432985265e-09f;
+__device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, float& s, float& c) {
+  const float r = x * c_hi;
+  const float k = rintf(r);
+  float fr = fmaf(x, c_hi, -k);
+  fr = fmaf(x, c_lo, fr);
+  const float ang = fr * 6.283185307179586f;
+  s = __sinf(ang);
+  c = __cosf(ang);
+}
+
+// The per-tile consumer view of its mask ring: blocks are produced (one producer lane per tile) and consumed by
+// the tile's 4 warps in one order: [init blocks] then, for every masked step, 4 blocks.
+struct MaskRing {
+  uint64_t* full;      // m_full[tile]
+  uint64_t* empty;     // m_empty[tile]
+  uint8_t* base;       // this tile's ring memory
+  uint32_t next;       // index of the next block of this tile
+  int lane;
+  __device__ __forceinline__ const uint8_t* acquire(uint32_t idx) {
+    mbar_wait(&full[idx % kMaskRing], (idx / kMaskRing) & 1u, 0x600 + (idx & 0xff));
+    return base + (idx % kMaskRing) * 16384;
+  }
+  __device__ __forceinline__ void release(uint32_t idx) {     // one arrive per warp (m_empty counts 4)
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[idx % kMaskRing]);
+  }
+};
+
+// Epilogue of a masked step (F, L7..L1): 256 accumulator columns -> (+ d_sigma * w_alpha for F) -> bf16 -> AND
+// with the ReLU mask of the saved activation -> next A operand (in place).
+template <bool ADD_ALPHA>
+__device__ __forceinline__ void epi_masked(uint32_t taddr, MaskRing& mr, uint32_t first_idx, float dsigma,
+                                           const float* __restrict__ s_walpha, uint8_t* sA, uint32_t row_base, uint32_t row_xor) {
+  uint32_t va[32], vb[32];
+  const uint8_t* hb = nullptr;
+  auto chunk = [&](const uint32_t (&v)[32], int c0) {
+    if ((c0 & 63) == 0) hb = mr.acquire(first_idx + (c0 >> 6));
+    uint32_t pk[16];
+#pragma unroll
+    for (int q4 = 0; q4 < 4; ++q4) {
+      const uint4 hw = load_chunk(hb, row_base, row_xor, ((c0 & 63) >> 3) + q4);
+      const uint32_t hws[4] = {hw.x, hw.y, hw.z, hw.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f0 = __uint_as_float(v[8 * q4 + 2 * j]), f1 = __uint_as_float(v[8 * q4 + 2 * j + 1]);
+        if (ADD_ALPHA) {
+          f0 = fmaf(dsigma, s_walpha[c0 + 8 * q4 + 2 * j], f0);
+          f1 = fmaf(dsigma, s_walpha[c0 + 8 * q4 + 2 * j + 1], f1);
+        }
+        pk[4 * q4 + j] = pack_bf16x2(f0, f1) & relu_mask2(hws[j]);
+      }
+    }
+    uint8_t* blk = sA + (c0 >> 6) * 16384;
+    const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    if ((c0 & 63) == 32) mr.release(first_idx + (c0 >> 6));
+  };
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    tmem_wait_ld();
+    tmem_ld32(taddr + (c + 1) * 32, vb);
+    chunk(va, c * 32);
+    tmem_wait_ld();
+    if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
+    chunk(vb, (c + 1) * 32);
+  }
+}
+
+// Epilogue of the linear step V1 (d feature): 256 columns -> bf16 -> A operand.
+__device__ __forceinline__ void epi_linear(uint32_t taddr, uint8_t* sA, uint32_t row_base, uint32_t row_xor) {
+  uint32_t va[32], vb[32];
+  auto chunk = [&](const uint32_t (&v)[32], int c0) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+    uint8_t* blk = sA + (c0 >> 6) * 16384;
+    const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  };
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    tmem_wait_ld();
+    tmem_ld32(taddr + (c + 1) * 32, vb);
+    chunk(va, c * 32);
+    tmem_wait_ld();
+    if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
+    chunk(vb, (c + 1) * 32);
+  }
+}
+
+struct DgradArgs {
+  RowSrc src;                       // rays + depths (FINE: needed for d PE -> d t); R, S define the row space
+  const float4* d_raw;              // [M] (d r, d g, d b, d sigma) w.r.t. the pre-activation outputs
+  const uint8_t* act_arena;         // saved forward activations (tc_arena.cuh)
+  uint8_t* grad_arena;              // out: dZ tile images
+  float4* pe_scratch;               // FINE: [M, 16] float4 -- d PE contribution of layer 5 (skip connection)
+  float* d_t;                       // FINE: [M] += d loss / d t
+  const __nv_bfloat16* wpack;       // dgrad stage images of this net
+  const float* P;                   // fp32 parameters of this net (heads)
+  int64_t M, n_pair;
+};
+
+template <bool FINE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2_dgrad_kernel(DgradArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
+  float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
+  float* s_wrgb = s_walpha + 256;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int64_t pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+  // step list of this net: the coarse net only receives d sigma: trunk only, no input gradient
+  constexpr int kSteps = FINE ? 11 : 7;
+  constexpr int kFineSteps[11] = {S_V1, S_F, S_L7, S_L6, S_PE5, S_L5, S_L4, S_L3, S_L2, S_L1, S_P0};
+  constexpr int kCoarseSteps[7] = {S_L7, S_L6, S_L5, S_L4, S_L3, S_L2, S_L1};
+  auto step_at = [&](int i) { return FINE ? kFineSteps[i] : kCoarseSteps[i]; };
+  constexpr int kInitBlocks = FINE ? 2 : 4;                                   // hv (2 blocks) / h7 (4 blocks)
+  constexpr int kInitSlot = FINE ? arena::kActHV : arena::kActH + 28;
+
+  if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA13, smem_u32(smem));
+  if (tid == 0) {
+    for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
+    for (int t = 0; t < 2; ++t)
+      for (int i = 0; i < kMaskRing; ++i) { mbar_init(&sb.m_full[t][i], 1); mbar_init(&sb.m_empty[t][i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
+    fence_barrier_init();
+  }
+  for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(a.P + w_off(L_ALPHA) + i);
+  for (int i = tid; i < 384; i += kThreads) s_wrgb[i] = __ldg(a.P + w_off(L_RGB) + i);
+  cluster_sync_all();
+  if (warp == 2) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sb.tmem_slot;
+
+  if (warp == 0) {
+    // ===== weight producer =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
+        for (int i = 0; i < kSteps; ++i) {
+          const int s = step_at(i);
+          const uint32_t bytes = (uint32_t)step_n(s) * 64u;
+          for (int kb = 0; kb < step_nkb(s); ++kb, ++it) {
+            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+            mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
+            mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
+            bulk_g2s(smem + kOffW + slot * kHalfBytes,
+                     reinterpret_cast<const uint8_t*>(a.wpack) + (size_t)(step_stage0(s) + kb) * kStageImage + (size_t)rank * bytes,
+                     bytes, &sb.w_full[slot]);
+          }
+        }
+    }
+    __syncwarp();
+  } else if (warp == 2 || warp == 3) {
+    // ===== mask producers: warp 2 feeds tile X's ring, warp 3 tile Y's, saved activation blocks in consumption order =====
+    if (lane == 0) {
+      const int t = warp - 2;
+      uint32_t it = 0;
+      auto push = [&](const uint8_t* src_block) {
+        const uint32_t slot = it % kMaskRing, par = (it / kMaskRing) & 1u;
+        mbar_wait(&sb.m_empty[t][slot], par ^ 1u, 0x700 + (it & 0xff));
+        mbar_arrive_expect_tx(&sb.m_full[t][slot], 16384u);
+        bulk_g2s(smem + kOffMask + (t * kMaskRing + slot) * 16384, src_block, 16384u, &sb.m_full[t][slot]);
+        ++it;
+      };
+      for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
+        const uint8_t* tb = a.act_arena + (size_t)((st * 2 + rank) * 2 + t) * arena::act_tile_bytes();
+        for (int b = 0; b < kInitBlocks; ++b) push(tb + (size_t)(kInitSlot + b) * arena::kBlockBytes);
+        for (int i = 0; i < kSteps; ++i) {
+          const int ms = step_mask_slot(step_at(i));
+          if (ms < 0) continue;
+          for (int b = 0; b < 4; ++b) push(tb + (size_t)(ms + b) * arena::kBlockBytes);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1 && rank == 1) {
+    // ===== forwarder =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
+        for (int i = 0; i < kSteps; ++i)
+          for (int kb = 0; kb < step_nkb(step_at(i)); ++kb, ++it) {
+            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+            mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
+            mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+          }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader) =====
+    if (lane == 0) {
+      uint32_t it = 0, lc = 0;
+      const uint32_t sA = smem_u32(smem + kOffA), sW = smem_u32(smem + kOffW);
+      for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
+        for (int i = 0; i < kSteps; ++i, ++lc) {
+          const int s = step_at(i), nkb = step_nkb(s);
+          const uint32_t idesc = make_idesc_bf16(256, step_n(s));
+          for (int kb = 0; kb < nkb; ++kb, ++it) {
+            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+            mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+            tc_fence_after();
+#pragma unroll
+            for (int tile = 0; tile < 2; ++tile) {
+              if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+              const uint32_t a_base = sA + tile * 65536u + (uint32_t)kb * 16384u;
+              const uint32_t b_base = sW + slot * kHalfBytes;
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
+                         make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+              if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+            }
+            umma_commit2(&sb.w_empty[slot], 0x3);
+          }
+        }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===== gradient warps: init step + per-step epilogues =====
+    const int tile = (warp - 4) >> 2, q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tile * 256u;
+    uint8_t* sA = smem + kOffA + tile * 65536;
+    const uint32_t row_base = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128), row_xor = (uint32_t)(row & 7);
+    const uint32_t ready_addr = mapa_u32(smem_u32(&sb.act_ready[tile]), 0);
+    const bool tile_leader = (q == 0 && lane == 0);
+    const uint32_t bar_id = 1 + tile;
+    MaskRing mr{sb.m_full[tile], sb.m_empty[tile], smem + kOffMask + tile * kMaskRing * 16384, 0u, lane};
+    auto signal_ready = [&]() {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(ready_addr);
+    };
+    auto before_overwrite = [&]() { if (tile_leader) bulk_wait_read0(); named_bar_sync(bar_id, kTile); };
+    auto save_blocks = [&](uint8_t* gtile, int slot, int nblocks) {
+      named_bar_sync(bar_id, kTile);
+      if (tile_leader) {
+        for (int b = 0; b < nblocks; ++b) bulk_s2g(gtile + (size_t)(slot + b) * arena::kBlockBytes, sA + b * 16384, arena::kBlockBytes);
+        bulk_commit();
+      }
+    };
+    uint32_t lc = 0;
+    for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
+      const int64_t T = (st * 2 + rank) * 2 + tile;
+      const int64_t g = T * kTile + row;
+      const bool valid = g < a.M;
+      uint8_t* gtile = a.grad_arena + (size_t)T * arena::grad_tile_bytes();
+      const float4 dr = valid ? __ldg(a.d_raw + g) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float p[3] = {0.f, 0.f, 0.f}, vd[3];
+      if (FINE && valid) row_point(a.src, g, p, vd);
+
+      // ---- init: the first A operand from d raw ----
+      before_overwrite();
+      {
+        const uint32_t first = mr.next;
+        for (int b = 0; b < kInitBlocks; ++b) {
+          const uint8_t* hb = mr.acquire(first + b);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const uint4 hw = load_chunk(hb, row_base, row_xor, ch);
+            const uint32_t hws[4] = {hw.x, hw.y, hw.z, hw.w};
+            uint32_t pk[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int c = b * 64 + ch * 8 + 2 * j;
+              float f0, f1;
+              if (FINE) {      // d hv_pre = W_rgb^T d rgb, masked by hv > 0   (rgb_linear.weight [3,128])
+                f0 = dr.x * s_wrgb[c] + dr.y * s_wrgb[128 + c] + dr.z * s_wrgb[256 + c];
+                f1 = dr.x * s_wrgb[c + 1] + dr.y * s_wrgb[128 + c + 1] + dr.z * s_wrgb[256 + c + 1];
+              } else {         // d h7 = w_alpha d sigma, masked by h7 > 0
+                f0 = dr.w * s_walpha[c]; f1 = dr.w * s_walpha[c + 1];
+              }
+              pk[j] = pack_bf16x2(f0, f1) & relu_mask2(hws[j]);
+            }
+            store_chunk(sA + b * 16384, row_base, row_xor, ch, pk[0], pk[1], pk[2], pk[3]);
+          }
+          mr.release(first + b);
+        }
+        mr.next += kInitBlocks;
+      }
+      signal_ready();
+      save_blocks(gtile, FINE ? arena::kGradHV : arena::kGradZ + 28, kInitBlocks);
+
+      for (int i = 0; i < kSteps; ++i, ++lc) {
+        const int s = step_at(i);
+        mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
+        tc_fence_after();
+        if (s == S_PE5) {
+          // d PE from the skip connection: park 64 fp32 columns in HBM until the end of the chain
+          uint32_t v[32];
+#pragma unroll
+          for (int hlf = 0; hlf < 2; ++hlf) {
+            tmem_ld32(taddr + hlf * 32, v);
+            tmem_wait_ld();
+            if (valid) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                a.pe_scratch[g * 16 + hlf * 8 + j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                                                __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            }
+          }
+          signal_ready();
+        } else if (s == S_P0) {
+          // d PE = dZ0 W0 + (layer-5 part) ; PE backward ; d t += d . d pts
+          float dpe[64];
+          uint32_t v[32];
+#pragma unroll
+          for (int hlf = 0; hlf < 2; ++hlf) {
+            tmem_ld32(taddr + hlf * 32, v);
+            tmem_wait_ld();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) dpe[hlf * 32 + j] = __uint_as_float(v[j]);
+          }
+          tc_fence_before();
+          if (valid) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float4 sc = a.pe_scratch[g * 16 + j];
+              dpe[4 * j] += sc.x; dpe[4 * j + 1] += sc.y; dpe[4 * j + 2] += sc.z; dpe[4 * j + 3] += sc.w;
+            }
+            const int64_t ray = g / a.src.S;
+            float acc = 0.f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              float dp = dpe[c];
+              float chi = kInv2PiHi, clo = kInv2PiLo, f = 1.0f;
+#pragma unroll
+              for (int k = 0; k < 10; ++k, chi *= 2.0f, clo *= 2.0f, f *= 2.0f) {
+                float sn, cs;
+                sincos_turns(p[c], chi, clo, sn, cs);
+                dp += f * (cs * dpe[3 + 6 * k + c] - sn * dpe[3 + 6 * k + 3 + c]);
+              }
+              acc += dp * __ldg(a.src.rays_d + 3 * ray + c);
+            }
+            a.d_t[g] += acc;
+          }
+        } else {
+          before_overwrite();
+          if (s == S_V1) epi_linear(taddr, sA, row_base, row_xor);
+          else {
+            const uint32_t first = mr.next;
+            if (s == S_F) epi_masked<true>(taddr, mr, first, dr.w, s_walpha, sA, row_base, row_xor);
+            else epi_masked<false>(taddr, mr, first, 0.f, s_walpha, sA, row_base, row_xor);
+            mr.next += 4;
+          }
+          if (i + 1 < kSteps) signal_ready(); else { fence_proxy_async_smem(); tc_fence_before(); }
+          save_blocks(gtile, step_out_slot(s), 4);
+        }
+      }
+    }
+    if (tile_leader) bulk_wait0();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc2(tmem, 512);
+}
+
+}  // namespace bw
+
+// d_raw [M,4] -> gradient arena (+ d_t for the fine net).  Row space and tiling identical to the saving forward.
+// full: all layers receive gradients and d_t is produced (fine net; coarse net when N_importance == 0);
+// !full: only d sigma arrives (coarse net of the hierarchical path): trunk + alpha only.
+int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const float* d_raw, const uint8_t* act_arena,
+                  uint8_t* grad_arena, float* pe_scratch, float* d_t, cudaStream_t st) {
+  using namespace bw;
+  const int64_t M = src.R * src.S;
+  if (M <= 0) return NERF_OK;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_tc2_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_tc2_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_dgrad smem attribute: ") + cudaGetErrorString(e));
+    attr_set = true;
+  }
+  DgradArgs a;
+  a.src = src; a.d_raw = reinterpret_cast<const float4*>(d_raw); a.act_arena = act_arena; a.grad_arena = grad_arena;
+  a.pe_scratch = reinterpret_cast<float4*>(pe_scratch); a.d_t = d_t;
+  a.wpack = h->wpack_bwd + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
+  a.P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
+  a.M = M; a.n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
+  const int grid = 2 * (int)std::min<int64_t>(a.n_pair, h->num_sms / 2);
+  if (full) mlp_tc2_dgrad_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
+  else mlp_tc2_dgrad_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
+  h->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string(full ? "mlp_tc2_dgrad<full> launch: " : "mlp_tc2_dgrad<sigma> launch: ") + cudaGetErrorString(e));
+  return NERF_OK;
+}
+
+
+// =====================================================================================================
+// part 2: weight gradients
+// =====================================================================================================
+namespace wg {
+
+constexpr int kThreads = 192;          // warp 0 producer, warp 1 MMA issuer / forwarder, warps 2-5 flush (TMEM lanes 0..127)
+constexpr int kStageBytes = 5 * 16384; // A' 2 blocks | B' main 2 blocks | B' extra 1 block
+constexpr int kStages = 2;
+constexpr uint32_t kOffStage = 0, kOffXpose = kStages * kStageBytes;          // 163840
+constexpr uint32_t kOffBar = kOffXpose + 4 * 32 * 33 * 4;                     // 180736
+constexpr uint32_t kSmemBytes = kOffBar + 128;
+constexpr int kNumJobsFine = 10, kNumJobsCoarse = 8;
+
+struct Job { int layer, a_slot, main_slot, extra_slot, main_col0, extra_col0, extra_ncols, out_dim; };
+__device__ __forceinline__ Job job_of(int j) {
+  Job b;
+  if (j < 8) {
+    b.layer = j; b.a_slot = arena::kGradZ + 4 * j;
+    b.main_slot = j == 0 ? -1 : (j == 5 ? arena::kActH + 16 : arena::kActH + 4 * (j - 1));
+    b.extra_slot = arena::kActPE; b.main_col0 = j == 5 ? 63 : 0; b.extra_col0 = 0;
+    b.extra_ncols = (j == 0 || j == 5) ? 63 : 0; b.out_dim = 256;
+  } else if (j == 8) {
+    b.layer = L_FEAT; b.a_slot = arena::kGradFeat; b.main_slot = arena::kActH + 28; b.extra_slot = arena::kActPE;
+    b.main_col0 = 0; b.extra_col0 = 0; b.extra_ncols = 0; b.out_dim = 256;
+  } else {
+    b.layer = L_VIEWS; b.a_slot = arena::kGradHV; b.main_slot = arena::kActFeat; b.extra_slot = arena::kActPEDir;
+    b.main_col0 = 0; b.extra_col0 = 256; b.extra_ncols = 27; b.out_dim = 128;
+  }
+  return b;
+}
+
+struct Bars { uint64_t full[kStages], empty[kStages], acc_done, tmem_free; uint32_t tmem_slot; };
+
+struct WgradArgs {
+  const uint8_t* act_arena; const uint8_t* grad_arena; float* G;     // G: flat gradient of this net (+=)
+  int n_tiles, chunk, n_jobs, n_units;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2_wgrad_kernel(WgradArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+  const int chunks = (a.n_tiles + a.chunk - 1) / a.chunk;
+
+  if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA14, smem_u32(smem));
+  if (tid == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&sb.full[i], rank == 0 ? 2 : 1); mbar_init(&sb.empty[i], 1); }
+    mbar_init(&sb.acc_done, 1); mbar_init(&sb.tmem_free, 8);
+    fence_barrier_init();
+  }
+  cluster_sync_all();
+  if (warp == 1) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sb.tmem_slot;
+
+  if (warp == 0) {
+    // ===== producer: per tile, my halves of dZ^T (A') and X^T (B' main) + the full extra block =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int u = pair0; u < a.n_units; u += pair_stride) {
+        const Job jb = job_of(u / chunks);
+        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        const int a_blk = jb.out_dim == 256 ? 2 * (int)rank : 0;       // views (128 outputs): both CTAs take blocks 0,1
+        for (int t = t0; t < t1; ++t, ++it) {
+          const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
+          mbar_wait(&sb.empty[slot], par ^ 1u, 0x10 + slot);
+          uint8_t* dst = smem + kOffStage + slot * kStageBytes;
+          const uint8_t* gt = a.grad_arena + (size_t)t * arena::grad_tile_bytes();
+          const uint8_t* at = a.act_arena + (size_t)t * arena::act_tile_bytes();
+          mbar_arrive_expect_tx(&sb.full[slot], (jb.main_slot >= 0 ? 5u : 3u) * 16384u);
+          bulk_g2s(dst, gt + (size_t)(jb.a_slot + a_blk) * 16384, 32768u, &sb.full[slot]);
+          if (jb.main_slot >= 0) bulk_g2s(dst + 32768, at + (size_t)(jb.main_slot + 2 * rank) * 16384, 32768u, &sb.full[slot]);
+          bulk_g2s(dst + 65536, at + (size_t)jb.extra_slot * 16384, 16384u, &sb.full[slot]);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1 && rank == 1) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int u = pair0; u < a.n_units; u += pair_stride) {
+        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        for (int t = t0; t < t1; ++t, ++it) {
+          const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
+          mbar_wait(&sb.full[slot], par, 0x50 + slot);
+          mbar_arrive_remote(mapa_u32(smem_u32(&sb.full[slot]), 0));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===== MMA issuer: D[256 x (256 | 128)] += dZ^T X over the tile's 128 rows (8 K-steps of 16 rows) =====
+    if (lane == 0) {
+      uint32_t it = 0, uc = 0;
+      const uint32_t idesc_main = make_idesc_bf16(256, 256, 1, 1), idesc_extra = make_idesc_bf16(256, 128, 1, 1);
+      for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
+        const Job jb = job_of(u / chunks);
+        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        if (uc > 0) { mbar_wait(&sb.tmem_free, (uc - 1) & 1u, 0x30); tc_fence_after(); }
+        for (int t = t0; t < t1; ++t, ++it) {
+          const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
+          mbar_wait(&sb.full[slot], par, 0x20 + slot);
+          tc_fence_after();
+          const uint32_t base = smem_u32(smem + kOffStage + slot * kStageBytes);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t acc = (t > t0 || ks > 0) ? 1u : 0u;
+            const uint64_t ad = make_smem_desc(base + ks * 2048, 16384, 1024, kLayoutSW128);
+            if (jb.main_slot >= 0)
+              umma_ss2(tmem, ad, make_smem_desc(base + 32768 + ks * 2048, 16384, 1024, kLayoutSW128), idesc_main, acc);
+            umma_ss2(tmem + 256, ad, make_smem_desc(base + 65536 + ks * 2048, 16384, 1024, kLayoutSW128), idesc_extra, acc);
+          }
+          umma_commit2(&sb.empty[slot], 0x3);
+        }
+        umma_commit2(&sb.acc_done, 0x3);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== flush warps: TMEM -> (transpose through shared memory) -> coalesced red.global.add =====
+    const int q = warp & 3;                    // TMEM lane quarter this warp may access
+    float* xp = reinterpret_cast<float*>(smem + kOffXpose) + q * 32 * 33;
+    const uint32_t free_addr = mapa_u32(smem_u32(&sb.tmem_free), 0);
+    uint32_t uc = 0;
+    for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
+      const Job jb = job_of(u / chunks);
+      mbar_wait(&sb.acc_done, uc & 1u, 0x40);
+      tc_fence_after();
+      const LayerDim d = layer_dim(jb.layer);
+      const int n_base = 128 * (int)rank + q * 32;              // first output row of this warp
+      const bool rows_valid = n_base < jb.out_dim;
+      float* Wg = a.G + w_off(jb.layer);
+      auto flush_cols = [&](int tcol0, int ncols, int gcol0) {   // D[:, tcol0 + c] -> dW[n][gcol0 + c], c < ncols
+        for (int c0 = 0; c0 < ncols; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + tcol0 + c0, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) xp[lane * 33 + j] = __uint_as_float(v[j]);
+          __syncwarp();
+          if (rows_valid && c0 + lane < ncols) {
+#pragma unroll 4
+            for (int r = 0; r < 32; ++r) atomicAdd(Wg + (size_t)(n_base + r) * d.in + gcol0 + c0 + lane, xp[r * 33 + lane]);
+          }
+          __syncwarp();
+        }
+      };
+      if (jb.main_slot >= 0) flush_cols(0, 256, jb.main_col0);
+      if (jb.extra_ncols > 0) flush_cols(256, jb.extra_ncols, jb.extra_col0);
+      {  // bias gradient: the "ones" column (63) of the extra block
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + 256 + 32, v);
+        tmem_wait_ld();
+        if (rows_valid) atomicAdd(a.G + b_off(jb.layer) + n_base + lane, __uint_as_float(v[31]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(free_addr);
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc2(tmem, 512);
+}
+
+// Heads on CUDA cores: alpha_linear (d sigma^T h7) and rgb_linear (d rgb^T hv) + their biases, straight from the
+// saved tile images.  One block per tile range, thread = column.
+__global__ void __launch_bounds__(256) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
+                                                          int64_t M, int n_tiles, int fine, float* __restrict__ G) {
+  const int c = threadIdx.x;
+  float acc_a = 0.f, acc_r[3] = {0.f, 0.f, 0.f}, bsum[4] = {0.f, 0.f, 0.f, 0.f};
+  __shared__ float4 s_dr[128];
+  for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    __syncthreads();
+    if (c < 128) { const int64_t g = (int64_t)t * 128 + c; s_dr[c] = g < M ? d_raw[g] : make_float4(0.f, 0.f, 0.f, 0.f); }
+    __syncthreads();
+    const uint8_t* at = act_arena + (size_t)t * arena::act_tile_bytes();
+    const uint8_t* h7 = at + (size_t)(arena::kActH + 28 + (c >> 6)) * 16384;
+    const uint8_t* hv = at + (size_t)(arena::kActHV + ((c & 127) >> 6)) * 16384;
+    for (int r = 0; r < 128; ++r) {
+      const float4 dr = s_dr[r];
+      const uint32_t off = sw128_offset(r, (c & 63) >> 3) + (c & 7) * 2;
+      acc_a = fmaf(dr.w, __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(h7 + off)), acc_a);
+      if (fine && c < 128) {
+        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(hv + off));
+        acc_r[0] = fmaf(dr.x, x, acc_r[0]); acc_r[1] = fmaf(dr.y, x, acc_r[1]); acc_r[2] = fmaf(dr.z, x, acc_r[2]);
+      }
+      if (c == 0) { bsum[0] += dr.x; bsum[1] += dr.y; bsum[2] += dr.z; bsum[3] += dr.w; }
+    }
+  }
+  atomicAdd(G + w_off(L_ALPHA) + c, acc_a);
+  if (fine && c < 128) for (int k = 0; k < 3; ++k) atomicAdd(G + w_off(L_RGB) + k * 128 + c, acc_r[k]);
+  if (c == 0) {
+    atomicAdd(G + b_off(L_ALPHA), bsum[3]);
+    if (fine) for (int k = 0; k < 3; ++k) atomicAdd(G + b_off(L_RGB) + k, bsum[k]);
+  }
+}
+
+}  // namespace wg
+
+// flat_grad_net += weight / bias gradients of one net from the arenas written by the saving forward and the dgrad chain.
+int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const uint8_t* act_arena, const uint8_t* grad_arena,
+                  float* flat_grad_net, cudaStream_t st) {
+  using namespace wg;
+  if (M <= 0) return NERF_OK;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_tc2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_wgrad smem attribute: ") + cudaGetErrorString(e));
+    attr_set = true;
+  }
+  WgradArgs a;
+  a.act_arena = act_arena; a.grad_arena = grad_arena; a.G = flat_grad_net;
+  a.n_tiles = (int)arena::num_tiles(M);
+  a.n_jobs = full ? kNumJobsFine : kNumJobsCoarse;
+  const int pairs = h->num_sms / 2;
+  // tile ranges sized so that the units fill the CTA pairs ~4 times over (load balance vs flush overhead)
+  a.chunk = std::max(4, (int)((int64_t)a.n_tiles * a.n_jobs / (4 * pairs) + 1));
+  a.n_units = a.n_jobs * ((a.n_tiles + a.chunk - 1) / a.chunk);
+  const int grid = 2 * std::min(a.n_units, pairs);
+  mlp_tc2_wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
+  wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms * 2), 256, 0, st>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M, a.n_tiles,
+                                                                         full ? 1 : 0, flat_grad_net);
+  h->launches += 2;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_wgrad launch: ") + cudaGetErrorString(e));
+  return NERF_OK;
+}
+
+NERF_TC_DEFINE_DEBUG_SINK(tc2b_set_debug_sink)
+
+}  // namespace nerf

@@ -220,6 +220,8 @@ umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt,
 
 }  // namespace nerf
 
+namespace nerf { NERF_TC_DEFINE_DEBUG_SINK(tcp_set_debug_sink) }
+
 extern "C" int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K, void* stream) {
   using namespace nerf;
   if (variant == 4) {   // a = At [K x 128], b = Bt [K x N]

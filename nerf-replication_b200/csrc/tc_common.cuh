@@ -14,6 +14,8 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // ---- debug watchdog: a deadlocked barrier traps instead of hanging the GPU -------------------------
 // g_tc_debug[0] = first failing code (barrier tag), [1] = blockIdx, [2] = extra
 static __device__ unsigned int g_tc_debug[8];   // one copy per translation unit
+// optional host-mapped copy (survives the trap that kills the context); set per translation unit by tc_set_debug_sink
+static __device__ unsigned int* g_tc_debug_host = nullptr;
 constexpr long long kWatchdogCycles = 6000000000LL;   // ~3-4 s at B200 clocks
 
 // ---- mbarrier ---------------------------------------------------------------------------------
@@ -39,8 +41,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 static __device__ __noinline__ void mbar_timeout(uint32_t tag, uint32_t parity) {
-  if (atomicCAS(&g_tc_debug[0], 0u, tag) == 0u) { g_tc_debug[1] = blockIdx.x; g_tc_debug[2] = threadIdx.x; g_tc_debug[3] = parity; }
+  // every waiter that times out logs itself (host-mapped: [8..24) = tag | warp << 12 | block << 16 | parity << 31),
+  // then lingers so that the other stuck waiters can log too before the trap kills the grid
+  // one log line per warp: the lowest active lane speaks
+  const bool speaker = (__ffs(__activemask()) - 1) == (int)(threadIdx.x & 31);
+  const unsigned int n = speaker ? atomicAdd(&g_tc_debug[4], 1u) : 1000u;
+  if (n == 0) {
+    g_tc_debug[0] = tag; g_tc_debug[1] = blockIdx.x; g_tc_debug[2] = threadIdx.x; g_tc_debug[3] = parity;
+  }
+  if (g_tc_debug_host) {
+    volatile unsigned int* hp = g_tc_debug_host;
+    if (n == 0) { hp[1] = blockIdx.x; hp[2] = threadIdx.x; hp[3] = parity; hp[0] = tag; }
+    if (n < 56) hp[8 + n] = tag | ((threadIdx.x >> 5) << 12) | (blockIdx.x << 16) | (parity << 31);
+  }
   __threadfence_system();
+  const long long t0 = clock64();
+  while (clock64() - t0 < 1500000000LL) { }
   __trap();
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag) {
@@ -51,6 +67,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
     if ((++spins & 0x3FFu) == 0 && clock64() - t0 > kWatchdogCycles) mbar_timeout(tag, parity);
   }
 }
+
+// host side: point this translation unit's watchdog at a host-mapped buffer
+#define NERF_TC_DEFINE_DEBUG_SINK(fn)                                                              \
+  void fn(unsigned int* mapped) { cudaMemcpyToSymbol(nerf::tc::g_tc_debug_host, &mapped, sizeof(mapped)); }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (UMMA / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

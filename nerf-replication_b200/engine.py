@@ -256,6 +256,6 @@ class Engine:
         return d
 
     def watchdog(self):
-        out = (C.c_uint * 8)()
+        out = (C.c_uint * 64)()      # [0..8): first record, [8..64): one word per stuck waiter
         self.lib.nerf_debug_tc_watchdog(out)
         return list(out)

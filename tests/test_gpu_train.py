@@ -148,3 +148,77 @@ def test_loss_curve_tracks_oracle(oracle):
         l_ref = tr.step(o, d, gt)
         l = float(ft.step(o.cuda(), d.cuda(), gt.cuda()))
         assert abs(l - l_ref) <= 1e-2 * l_ref, (s, l, l_ref)
+
+
+def _grad_report(oracle, got, ref):
+    rows = []
+    ref_t, got_t = _per_tensor(oracle, ref), _per_tensor(oracle, got)
+    for k in ref_t:
+        scale = float(ref_t[k].abs().max())
+        err = maxabs(got_t[k], ref_t[k])
+        rows.append((k, err, scale, err / scale if scale > 0 else (0.0 if err == 0 else float("inf"))))
+    return rows
+
+
+@pytest.mark.parametrize("weights", ["fog", "sharp"])
+def test_bf16_tensor_core_backward_vs_oracle(oracle, weights):
+    """bf16 training path: saving forward (tcgen05) + dgrad chain + wgrad kernels vs torch autograd on the oracle with
+    the same bf16-representable weights.  Operands (activations, dZ) are bf16, accumulation fp32; the rounding of the
+    gradient tiles compounds through the chain (measured on B200: 0.1% of max at rgb_linear, 1% at layers 5-7, 4% at
+    layer 0), so fine-net tensors are held to 6e-2 of each tensor's max and a cosine similarity >= 0.999; the coarse
+    net's gradient (amplified through the inverse CDF, see the fp32 test) to 0.15 / cos >= 0.99 on the fog set."""
+    sd0 = oracle.fog_state_dict(0) if weights == "fog" else oracle.init_state_dict(0, sharp=True)
+    sd = oracle.round_weights_bf16(sd0)
+    n = 64
+    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, n, 100, 100)
+    tr = oracle.Trainer(sd)
+    loss_ref = tr.forward_backward(o, d, gt)
+    g_ref = tr.grads_flat()
+    eng = make_engine(oracle, sd, "bf16")
+    grad = torch.zeros(1191688, device="cuda")
+    loss = eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad)
+    torch.cuda.synchronize()
+    rep = _grad_report(oracle, grad.cpu(), g_ref)
+    for k, err, scale, rel in rep:
+        print("%-36s err %.3e  scale %.3e  rel %.3e" % (k, err, scale, rel))
+    print("loss", float(loss), float(loss_ref), eng.watchdog())
+    assert abs(float(loss) - float(loss_ref)) <= 2e-3 * float(loss_ref)
+    bad = []
+    for k, err, scale, rel in rep:
+        coarse = k.startswith("model.")
+        if coarse and any(s in k for s in ("views_linears", "feature_linear", "rgb_linear")):
+            if err != 0.0:
+                bad.append((k, err, scale))
+            continue
+        a, b = _per_tensor(oracle, grad.cpu())[k].double(), _per_tensor(oracle, g_ref)[k].double()
+        cos = float((a * b).sum() / (a.norm() * b.norm() + 1e-300))
+        if coarse and weights == "sharp":
+            continue                                     # noise-dominated in the fp32 reference itself (see above)
+        tol, cmin = (0.15, 0.99) if coarse else (6e-2, 0.999)
+        if rel > tol or cos < cmin:
+            bad.append((k, err, scale, rel, cos))
+    assert not bad, bad
+    eng.close()
+
+
+def test_bf16_loss_curve_tracks_oracle(oracle):
+    """bf16 tensor-core training (fp32 master weights, fused clip+Adam) vs the fp32 oracle: loss within 1% per step."""
+    from nerf_replication_b200 import config as C
+    from nerf_replication_b200.network import Network
+    from nerf_replication_b200.trainer import FusedTrainer
+    cfg = C.default_cfg()
+    sd = oracle.init_state_dict(0)
+    net = Network(cfg=cfg, precision="bf16")
+    net.load_state_dict(sd)
+    net = net.cuda()
+    ft = FusedTrainer(net, cfg=cfg)
+    tr = oracle.Trainer(sd)
+    torch.set_num_threads(8)
+    worst = 0.0
+    for s in range(40):
+        o, d, gt, _, _ = oracle.synthetic_train_batch(s, 0, 64, 100, 100)
+        l_ref = tr.step(o, d, gt)
+        l = float(ft.step(o.cuda(), d.cuda(), gt.cuda()))
+        worst = max(worst, abs(l - l_ref) / l_ref)
+        assert abs(l - l_ref) <= 1e-2 * l_ref, (s, l, l_ref)
+    print("bf16 loss curve: worst relative deviation over 40 steps = %.3e" % worst)
