@@ -89,6 +89,8 @@ int64_t nerf_launch_count(const NerfEngine* h);
  * last read, and resets the counters. */
 int nerf_profile_enable(NerfEngine* h, int on);
 int nerf_profile_read(NerfEngine* h, double* mlp_ms, int64_t* mlp_launches, int64_t* mlp_rows);
+/* same, per kernel class (arrays of 3): 0 = fused MLP forward, 1 = dgrad chain, 2 = wgrad (+ heads). */
+int nerf_profile_read_classes(NerfEngine* h, double* ms3, int64_t* launches3, int64_t* rows3);
 
 /* ---- stage kernels (parity taps; each is also used by the fused calls) ------------------------- */
 /* a-B get_rays, src/datasets/nerf/blender.py:95-127.  c2w_host: 12 doubles (3x4 row-major).  pixel_ids

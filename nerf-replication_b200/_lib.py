@@ -36,6 +36,7 @@ SIGNATURES = {
     "nerf_launch_count": (_L, [_P]),
     "nerf_profile_enable": (_I, [_P, _I]),
     "nerf_profile_read": (_I, [_P, C.POINTER(_D), C.POINTER(_L), C.POINTER(_L)]),
+    "nerf_profile_read_classes": (_I, [_P, C.POINTER(_D), C.POINTER(_L), C.POINTER(_L)]),
     "nerf_get_rays": (_I, [_P, C.POINTER(_D), _I, _I, _D, _D, _D, _P, _L, _L, _P, _P, _P]),
     "nerf_stratified_t": (_I, [_P, _L, _I, _P, _P, _P]),
     "nerf_freq_encode": (_I, [_P, _P, _L, _I, _P, _P]),

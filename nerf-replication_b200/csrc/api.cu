@@ -169,7 +169,7 @@ static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool k
   }
   if (h->profiling) cudaEventRecord(h->prof_event(), st);
   const int rc = (h->tc_variant == 1 && !keep) ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, act, st);
-  if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; }
+  if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; h->prof_class.push_back(0); h->prof_class_rows.push_back(src.R * src.S); }
   return rc;
 }
 
@@ -179,20 +179,34 @@ extern "C" int nerf_profile_enable(NerfEngine* h, int on) {
   return NERF_OK;
 }
 
-extern "C" int nerf_profile_read(NerfEngine* h, double* mlp_ms, int64_t* mlp_launches, int64_t* mlp_rows) {
+extern "C" int nerf_profile_read_classes(NerfEngine* h, double* ms3, int64_t* launches3, int64_t* rows3) {
   if (!h) return NERF_E_INVALID;
   cudaSetDevice(h->device);
   NERF_CUDA_TRY(h, cudaDeviceSynchronize());
-  double ms = 0.0;
+  double ms[3] = {0, 0, 0};
+  int64_t n[3] = {0, 0, 0}, rows[3] = {0, 0, 0};
   for (size_t i = 0; i + 1 < h->prof_used; i += 2) {
     float t = 0.f;
     NERF_CUDA_TRY(h, cudaEventElapsedTime(&t, h->prof_pool[i], h->prof_pool[i + 1]));
-    ms += t;
+    const int c = i / 2 < h->prof_class.size() ? h->prof_class[i / 2] : 0;
+    ms[c] += t; n[c]++; rows[c] += i / 2 < h->prof_class_rows.size() ? h->prof_class_rows[i / 2] : 0;
   }
-  if (mlp_ms) *mlp_ms = ms;
-  if (mlp_launches) *mlp_launches = (int64_t)(h->prof_used / 2);
-  if (mlp_rows) *mlp_rows = h->prof_rows;
-  h->prof_used = 0; h->prof_rows = 0;
+  for (int c = 0; c < 3; ++c) {
+    if (ms3) ms3[c] = ms[c];
+    if (launches3) launches3[c] = n[c];
+    if (rows3) rows3[c] = rows[c];
+  }
+  h->prof_used = 0; h->prof_rows = 0; h->prof_class.clear(); h->prof_class_rows.clear();
+  return NERF_OK;
+}
+
+extern "C" int nerf_profile_read(NerfEngine* h, double* mlp_ms, int64_t* mlp_launches, int64_t* mlp_rows) {
+  double ms[3]; int64_t n[3], rows[3];
+  const int rc = nerf_profile_read_classes(h, ms, n, rows);
+  if (rc) return rc;
+  if (mlp_ms) *mlp_ms = ms[0];
+  if (mlp_launches) *mlp_launches = n[0];
+  if (mlp_rows) *mlp_rows = rows[0];
   return NERF_OK;
 }
 
@@ -423,8 +437,17 @@ static int mlp_backward(NerfEngine* h, int net, const RowSrc& src, const float* 
   if (full && !d_t) {   // coarse-only rendering: the input gradient is not needed; give the kernel a sink
     if ((rc = h->buf("tc.dt_sink", (size_t)M, &d_t))) return rc;
   }
+  auto mark = [&](int cls) {
+    if (!h->profiling) return;
+    cudaEventRecord(h->prof_event(), st);
+    if (cls >= 0) { h->prof_class.push_back(cls); h->prof_class_rows.push_back(M); }
+  };
+  mark(-1);
   if ((rc = mlp_tc2_dgrad(h, net, full, src, d_raw, act, grad, scratch, d_t, st))) return rc;
-  return mlp_tc2_wgrad(h, full, M, d_raw, act, grad, G, st);
+  mark(1); mark(-1);
+  rc = mlp_tc2_wgrad(h, full, M, d_raw, act, grad, G, st);
+  mark(2);
+  return rc;
 }
 
 static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,

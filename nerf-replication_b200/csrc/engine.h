@@ -38,6 +38,8 @@ struct NerfEngine {
   std::vector<cudaEvent_t> prof_pool;      // all events ever created (reused)
   size_t prof_used = 0;                    // events handed out since the last read (pairs: begin, end)
   int64_t prof_rows = 0;
+  std::vector<int> prof_class;             // class of each bracketed launch: 0 MLP forward, 1 dgrad chain, 2 wgrad
+  std::vector<int64_t> prof_class_rows;
   cudaEvent_t prof_event() {
     if (prof_used == prof_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); prof_pool.push_back(e); }
     return prof_pool[prof_used++];

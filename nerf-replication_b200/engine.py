@@ -101,6 +101,12 @@ class Engine:
         self._check(self.lib.nerf_profile_read(self.h, C.byref(ms), C.byref(n), C.byref(rows)))
         return ms.value, n.value, rows.value
 
+    def profile_read_classes(self):
+        """-> {"fwd"|"dgrad"|"wgrad": (ms, launches, rows)} since the last read; synchronises."""
+        ms, n, rows = (C.c_double * 3)(), (C.c_int64 * 3)(), (C.c_int64 * 3)()
+        self._check(self.lib.nerf_profile_read_classes(self.h, ms, n, rows))
+        return {k: (ms[i], n[i], rows[i]) for i, k in enumerate(("fwd", "dgrad", "wgrad"))}
+
     # -- parameters -----------------------------------------------------------------------------
     def set_params(self, flat):
         """flat: fp32 CUDA tensor [NERF_PARAMS_TOTAL] in state_dict order; kept alive by the engine."""
