@@ -12,6 +12,8 @@
 //
 // Reference graph: autograd of network.py:49-74 as exercised by trainers/nerf.py:27-33: the fine
 // net needs all weight gradients and the input gradient down to t; the coarse net only receives d sigma.
+#include <algorithm>
+#include <vector>
 #include "engine.h"
 #include "tc_common.cuh"
 #include "rows.cuh"
@@ -524,11 +526,14 @@ int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const fl
 // =====================================================================================================
 namespace wg {
 
-constexpr int kThreads = 192;          // warp 0 producer, warp 1 MMA issuer / forwarder, warps 2-5 flush (TMEM lanes 0..127)
-constexpr int kStageBytes = 5 * 16384; // A' 2 blocks | B' main 2 blocks | B' extra 1 block
-constexpr int kStages = 2;
+constexpr int kFlushWarps = 8;         // two warps per TMEM lane quarter, each flushing half of the columns
+constexpr int kThreads = 64 + 32 * kFlushWarps;   // warp 0 producer, warp 1 MMA issuer / forwarder, warps 2-9 flush
+constexpr int kHalfRows = 64;          // one ring stage = 64 of a tile's 128 rows (the first / second 8 KB of every block)
+constexpr int kPiece = 8192;
+constexpr int kStageBytes = 5 * kPiece;   // A' 2 pieces | B' main 2 pieces | B' extra 1 piece
+constexpr int kStages = 4;
 constexpr uint32_t kOffStage = 0, kOffXpose = kStages * kStageBytes;          // 163840
-constexpr uint32_t kOffBar = kOffXpose + 4 * 32 * 33 * 4;                     // 180736
+constexpr uint32_t kOffBar = kOffXpose + kFlushWarps * 32 * 33 * 4;           // 197632
 constexpr uint32_t kSmemBytes = kOffBar + 128;
 constexpr int kNumJobsFine = 10, kNumJobsCoarse = 8;
 
@@ -549,6 +554,8 @@ __device__ __forceinline__ Job job_of(int j) {
   }
   return b;
 }
+// relative cost of one tile of a job (bytes a pair streams), used by the host to size the tile ranges
+inline double job_weight(int j) { return j == 0 ? 0.6 : j == 9 ? 0.7 : 1.0; }
 
 struct Bars { uint64_t full[kStages], empty[kStages], acc_done, tmem_free; uint32_t tmem_slot; };
 
@@ -557,18 +564,18 @@ struct WgradArgs {
   int n_tiles, chunk, n_jobs, n_units;
 };
 
+// unit u = (job u % n_jobs, tile range u / n_jobs): pairs that flush at the same time hit different layers' dW
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2_wgrad_kernel(WgradArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = cluster_ctarank();
   const int pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
-  const int chunks = (a.n_tiles + a.chunk - 1) / a.chunk;
 
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA14, smem_u32(smem));
   if (tid == 0) {
     for (int i = 0; i < kStages; ++i) { mbar_init(&sb.full[i], rank == 0 ? 2 : 1); mbar_init(&sb.empty[i], 1); }
-    mbar_init(&sb.acc_done, 1); mbar_init(&sb.tmem_free, 8);
+    mbar_init(&sb.acc_done, 1); mbar_init(&sb.tmem_free, 2 * kFlushWarps);
     fence_barrier_init();
   }
   cluster_sync_all();
@@ -579,23 +586,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   const uint32_t tmem = sb.tmem_slot;
 
   if (warp == 0) {
-    // ===== producer: per tile, my halves of dZ^T (A') and X^T (B' main) + the full extra block =====
+    // ===== producer: per half tile, my halves of dZ^T (A') and X^T (B' main) + the full extra block =====
     if (lane == 0) {
       uint32_t it = 0;
       for (int u = pair0; u < a.n_units; u += pair_stride) {
-        const Job jb = job_of(u / chunks);
-        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        const Job jb = job_of(u % a.n_jobs);
+        const int t0 = (u / a.n_jobs) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
         const int a_blk = jb.out_dim == 256 ? 2 * (int)rank : 0;       // views (128 outputs): both CTAs take blocks 0,1
-        for (int t = t0; t < t1; ++t, ++it) {
-          const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
-          mbar_wait(&sb.empty[slot], par ^ 1u, 0x10 + slot);
-          uint8_t* dst = smem + kOffStage + slot * kStageBytes;
-          const uint8_t* gt = a.grad_arena + (size_t)t * arena::grad_tile_bytes();
+        for (int t = t0; t < t1; ++t) {
+          const uint8_t* gt = a.grad_arena + (size_t)t * arena::grad_tile_bytes() + (size_t)(jb.a_slot + a_blk) * 16384;
           const uint8_t* at = a.act_arena + (size_t)t * arena::act_tile_bytes();
-          mbar_arrive_expect_tx(&sb.full[slot], (jb.main_slot >= 0 ? 5u : 3u) * 16384u);
-          bulk_g2s(dst, gt + (size_t)(jb.a_slot + a_blk) * 16384, 32768u, &sb.full[slot]);
-          if (jb.main_slot >= 0) bulk_g2s(dst + 32768, at + (size_t)(jb.main_slot + 2 * rank) * 16384, 32768u, &sb.full[slot]);
-          bulk_g2s(dst + 65536, at + (size_t)jb.extra_slot * 16384, 16384u, &sb.full[slot]);
+          const uint8_t* mt = at + (size_t)(jb.main_slot + 2 * (int)rank) * 16384;
+          const uint8_t* xt = at + (size_t)jb.extra_slot * 16384;
+          for (int hf = 0; hf < 2; ++hf, ++it) {
+            const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
+            mbar_wait(&sb.empty[slot], par ^ 1u, 0x10 + slot);
+            uint8_t* dst = smem + kOffStage + slot * kStageBytes;
+            const uint32_t o = hf * kPiece;
+            mbar_arrive_expect_tx(&sb.full[slot], (jb.main_slot >= 0 ? 5u : 3u) * kPiece);
+            bulk_g2s(dst, gt + o, kPiece, &sb.full[slot]);
+            bulk_g2s(dst + kPiece, gt + 16384 + o, kPiece, &sb.full[slot]);
+            if (jb.main_slot >= 0) {
+              bulk_g2s(dst + 2 * kPiece, mt + o, kPiece, &sb.full[slot]);
+              bulk_g2s(dst + 3 * kPiece, mt + 16384 + o, kPiece, &sb.full[slot]);
+            }
+            bulk_g2s(dst + 4 * kPiece, xt + o, kPiece, &sb.full[slot]);
+          }
         }
       }
     }
@@ -604,8 +620,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     if (lane == 0) {
       uint32_t it = 0;
       for (int u = pair0; u < a.n_units; u += pair_stride) {
-        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
-        for (int t = t0; t < t1; ++t, ++it) {
+        const int t0 = (u / a.n_jobs) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        for (int k = 2 * (t1 - t0); k > 0; --k, ++it) {
           const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
           mbar_wait(&sb.full[slot], par, 0x50 + slot);
           mbar_arrive_remote(mapa_u32(smem_u32(&sb.full[slot]), 0));
@@ -614,26 +630,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ===== MMA issuer: D[256 x (256 | 128)] += dZ^T X over the tile's 128 rows (8 K-steps of 16 rows) =====
+    // ===== MMA issuer: D[256 x (256 | 128)] += dZ^T X, 4 K-steps of 16 rows per half tile =====
     if (lane == 0) {
       uint32_t it = 0, uc = 0;
       const uint32_t idesc_main = make_idesc_bf16(256, 256, 1, 1), idesc_extra = make_idesc_bf16(256, 128, 1, 1);
       for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
-        const Job jb = job_of(u / chunks);
-        const int t0 = (u % chunks) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
+        const Job jb = job_of(u % a.n_jobs);
+        const int t0 = (u / a.n_jobs) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
         if (uc > 0) { mbar_wait(&sb.tmem_free, (uc - 1) & 1u, 0x30); tc_fence_after(); }
-        for (int t = t0; t < t1; ++t, ++it) {
+        const uint32_t it0 = it;
+        for (int k = 2 * (t1 - t0); k > 0; --k, ++it) {
           const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
           mbar_wait(&sb.full[slot], par, 0x20 + slot);
           tc_fence_after();
           const uint32_t base = smem_u32(smem + kOffStage + slot * kStageBytes);
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint32_t acc = (t > t0 || ks > 0) ? 1u : 0u;
-            const uint64_t ad = make_smem_desc(base + ks * 2048, 16384, 1024, kLayoutSW128);
+          for (int ks = 0; ks < kHalfRows / 16; ++ks) {
+            const uint32_t acc = (it > it0 || ks > 0) ? 1u : 0u;
+            const uint64_t ad = make_smem_desc(base + ks * 2048, kPiece, 1024, kLayoutSW128);
             if (jb.main_slot >= 0)
-              umma_ss2(tmem, ad, make_smem_desc(base + 32768 + ks * 2048, 16384, 1024, kLayoutSW128), idesc_main, acc);
-            umma_ss2(tmem + 256, ad, make_smem_desc(base + 65536 + ks * 2048, 16384, 1024, kLayoutSW128), idesc_extra, acc);
+              umma_ss2(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 2048, kPiece, 1024, kLayoutSW128), idesc_main, acc);
+            umma_ss2(tmem + 256, ad, make_smem_desc(base + 4 * kPiece + ks * 2048, kPiece, 1024, kLayoutSW128), idesc_extra, acc);
           }
           umma_commit2(&sb.empty[slot], 0x3);
         }
@@ -643,20 +660,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     __syncwarp();
   } else {
     // ===== flush warps: TMEM -> (transpose through shared memory) -> coalesced red.global.add =====
-    const int q = warp & 3;                    // TMEM lane quarter this warp may access
-    float* xp = reinterpret_cast<float*>(smem + kOffXpose) + q * 32 * 33;
+    const int fw = warp - 2, q = warp & 3, hsel = fw >> 2;   // TMEM lane quarter this warp may access; column half
+    float* xp = reinterpret_cast<float*>(smem + kOffXpose) + fw * 32 * 33;
     const uint32_t free_addr = mapa_u32(smem_u32(&sb.tmem_free), 0);
     uint32_t uc = 0;
     for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
-      const Job jb = job_of(u / chunks);
+      const Job jb = job_of(u % a.n_jobs);
       mbar_wait(&sb.acc_done, uc & 1u, 0x40);
       tc_fence_after();
       const LayerDim d = layer_dim(jb.layer);
       const int n_base = 128 * (int)rank + q * 32;              // first output row of this warp
       const bool rows_valid = n_base < jb.out_dim;
       float* Wg = a.G + w_off(jb.layer);
-      auto flush_cols = [&](int tcol0, int ncols, int gcol0) {   // D[:, tcol0 + c] -> dW[n][gcol0 + c], c < ncols
-        for (int c0 = 0; c0 < ncols; c0 += 32) {
+      auto flush_cols = [&](int tcol0, int c_begin, int c_end, int ncols, int gcol0) {   // D[:, tcol0 + c] -> dW[n][gcol0 + c]
+        for (int c0 = c_begin; c0 < c_end && c0 < ncols; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + tcol0 + c0, v);
           tmem_wait_ld();
@@ -664,15 +681,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           for (int j = 0; j < 32; ++j) xp[lane * 33 + j] = __uint_as_float(v[j]);
           __syncwarp();
           if (rows_valid && c0 + lane < ncols) {
-#pragma unroll 4
+#pragma unroll 8
             for (int r = 0; r < 32; ++r) atomicAdd(Wg + (size_t)(n_base + r) * d.in + gcol0 + c0 + lane, xp[r * 33 + lane]);
           }
           __syncwarp();
         }
       };
-      if (jb.main_slot >= 0) flush_cols(0, 256, jb.main_col0);
-      if (jb.extra_ncols > 0) flush_cols(256, jb.extra_ncols, jb.extra_col0);
-      {  // bias gradient: the "ones" column (63) of the extra block
+      if (jb.main_slot >= 0) flush_cols(0, 128 * hsel, 128 * hsel + 128, 256, jb.main_col0);
+      if (jb.extra_ncols > 0) flush_cols(256, 32 * hsel, 32 * hsel + 32, jb.extra_ncols, jb.extra_col0);
+      if (hsel == 1) {  // bias gradient: the "ones" column (63) of the extra block
         uint32_t v[32];
         tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + 256 + 32, v);
         tmem_wait_ld();
@@ -689,36 +706,90 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 }
 
 // Heads on CUDA cores: alpha_linear (d sigma^T h7) and rgb_linear (d rgb^T hv) + their biases, straight from the
-// saved tile images.  One block per tile range, thread = column.
-__global__ void __launch_bounds__(256) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
+// saved tile images.  Warp w streams head block w of every tile of its CTA (0..3: h7, 4..5: hv); a lane owns one
+// logical 16-byte chunk (8 columns) of every fourth row, so a warp instruction reads four whole 128-byte rows.
+__global__ void __launch_bounds__(192) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
                                                           int64_t M, int n_tiles, int fine, float* __restrict__ G) {
-  const int c = threadIdx.x;
-  float acc_a = 0.f, acc_r[3] = {0.f, 0.f, 0.f}, bsum[4] = {0.f, 0.f, 0.f, 0.f};
-  __shared__ float4 s_dr[128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = lane & 7, rs = lane >> 3;
+  const bool is_rgb = warp >= 4;
+  if (is_rgb && !fine) return;
+  const int slot = is_rgb ? arena::kActHV + (warp - 4) : arena::kActH + 28 + warp;
+  float acc[3][8], bs[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
   for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-    __syncthreads();
-    if (c < 128) { const int64_t g = (int64_t)t * 128 + c; s_dr[c] = g < M ? d_raw[g] : make_float4(0.f, 0.f, 0.f, 0.f); }
-    __syncthreads();
-    const uint8_t* at = act_arena + (size_t)t * arena::act_tile_bytes();
-    const uint8_t* h7 = at + (size_t)(arena::kActH + 28 + (c >> 6)) * 16384;
-    const uint8_t* hv = at + (size_t)(arena::kActHV + ((c & 127) >> 6)) * 16384;
-    for (int r = 0; r < 128; ++r) {
-      const float4 dr = s_dr[r];
-      const uint32_t off = sw128_offset(r, (c & 63) >> 3) + (c & 7) * 2;
-      acc_a = fmaf(dr.w, __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(h7 + off)), acc_a);
-      if (fine && c < 128) {
-        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(hv + off));
-        acc_r[0] = fmaf(dr.x, x, acc_r[0]); acc_r[1] = fmaf(dr.y, x, acc_r[1]); acc_r[2] = fmaf(dr.z, x, acc_r[2]);
+    const uint8_t* blk = act_arena + (size_t)t * arena::act_tile_bytes() + (size_t)slot * 16384;
+    const int64_t g0 = (int64_t)t * 128;
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) {
+      const int r = 4 * i + rs;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(blk + sw128_offset(r, j)));
+      const float4 dr = g0 + r < M ? __ldg(d_raw + g0 + r) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float x0 = __uint_as_float(w[e] << 16), x1 = __uint_as_float(w[e] & 0xFFFF0000u);
+        if (is_rgb) {
+          acc[0][2 * e] = fmaf(dr.x, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.x, x1, acc[0][2 * e + 1]);
+          acc[1][2 * e] = fmaf(dr.y, x0, acc[1][2 * e]); acc[1][2 * e + 1] = fmaf(dr.y, x1, acc[1][2 * e + 1]);
+          acc[2][2 * e] = fmaf(dr.z, x0, acc[2][2 * e]); acc[2][2 * e + 1] = fmaf(dr.z, x1, acc[2][2 * e + 1]);
+        } else {
+          acc[0][2 * e] = fmaf(dr.w, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.w, x1, acc[0][2 * e + 1]);
+        }
       }
-      if (c == 0) { bsum[0] += dr.x; bsum[1] += dr.y; bsum[2] += dr.z; bsum[3] += dr.w; }
+      if (j == 0) { bs[0] += dr.x; bs[1] += dr.y; bs[2] += dr.z; bs[3] += dr.w; }
     }
   }
-  atomicAdd(G + w_off(L_ALPHA) + c, acc_a);
-  if (fine && c < 128) for (int k = 0; k < 3; ++k) atomicAdd(G + w_off(L_RGB) + k * 128 + c, acc_r[k]);
-  if (c == 0) {
-    atomicAdd(G + b_off(L_ALPHA), bsum[3]);
-    if (fine) for (int k = 0; k < 3; ++k) atomicAdd(G + b_off(L_RGB) + k, bsum[k]);
+  // fold the four row groups (lanes l, l^8, l^16, l^24)
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      acc[k][e] += __shfl_xor_sync(0xffffffffu, acc[k][e], 8);
+      acc[k][e] += __shfl_xor_sync(0xffffffffu, acc[k][e], 16);
+    }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    bs[k] += __shfl_xor_sync(0xffffffffu, bs[k], 8);
+    bs[k] += __shfl_xor_sync(0xffffffffu, bs[k], 16);
   }
+  if (rs == 0) {
+    if (is_rgb) {
+      const int c0 = (warp - 4) * 64 + 8 * j;
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(G + w_off(L_RGB) + k * 128 + c0 + e, acc[k][e]);
+      if (warp == 4 && j == 0) for (int k = 0; k < 3; ++k) atomicAdd(G + b_off(L_RGB) + k, bs[k]);
+    } else {
+      const int c0 = warp * 64 + 8 * j;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(G + w_off(L_ALPHA) + c0 + e, acc[0][e]);
+      if (warp == 0 && j == 0) atomicAdd(G + b_off(L_ALPHA), bs[3]);
+    }
+  }
+}
+
+// Tile-range length: units (job, range) are dealt round-robin to the CTA pairs; pick the range length that minimises the
+// busiest pair's work, one flush costing about kFlushTiles tile-loads.
+static int pick_chunk(int n_tiles, int n_jobs, int pairs) {
+  constexpr double kFlushTiles = 10.0;
+  double best = 1e300; int best_chunk = n_tiles;
+  std::vector<double> load(pairs);
+  for (int chunk = std::min(n_tiles, 8); chunk <= n_tiles; ++chunk) {
+    const int ranges = (n_tiles + chunk - 1) / chunk, units = n_jobs * ranges;
+    std::fill(load.begin(), load.end(), 0.0);
+    for (int u = 0; u < units; ++u) {
+      const int t0 = (u / n_jobs) * chunk, len = std::min(chunk, n_tiles - t0);
+      load[u % pairs] += job_weight(u % n_jobs) * len + kFlushTiles;
+    }
+    const double mk = *std::max_element(load.begin(), load.end());
+    if (mk < best) { best = mk; best_chunk = chunk; }
+  }
+  return best_chunk;
 }
 
 }  // namespace wg
@@ -739,13 +810,14 @@ int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const
   a.n_tiles = (int)arena::num_tiles(M);
   a.n_jobs = full ? kNumJobsFine : kNumJobsCoarse;
   const int pairs = h->num_sms / 2;
-  // tile ranges sized so that the units fill the CTA pairs ~4 times over (load balance vs flush overhead)
-  a.chunk = std::max(4, (int)((int64_t)a.n_tiles * a.n_jobs / (4 * pairs) + 1));
+  static int memo_tiles[2] = {-1, -1}, memo_chunk[2] = {0, 0};
+  if (memo_tiles[full] != a.n_tiles) { memo_tiles[full] = a.n_tiles; memo_chunk[full] = pick_chunk(a.n_tiles, a.n_jobs, pairs); }
+  a.chunk = memo_chunk[full];
   a.n_units = a.n_jobs * ((a.n_tiles + a.chunk - 1) / a.chunk);
   const int grid = 2 * std::min(a.n_units, pairs);
   mlp_tc2_wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
-  wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms * 2), 256, 0, st>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M, a.n_tiles,
-                                                                         full ? 1 : 0, flat_grad_net);
+  wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms * 4), 192, 0, st>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M,
+                                                                         a.n_tiles, full ? 1 : 0, flat_grad_net);
   h->launches += 2;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_wgrad launch: ") + cudaGetErrorString(e));

@@ -78,5 +78,25 @@ def source(rep, top=40):
                                                           ", ".join("%s=%d" % (n, c) for c, n in st if c)))
 
 
+def lines(rep, launch="0", top=40):
+    """CUDA source lines by stall samples (needs -lineinfo + --import-source on)."""
+    rows = ncu_csv(rep, "source", ["--launch-skip", launch, "--launch-count", "1", "--print-source", "cuda,sass"])
+    path, out, H = "?", [], None
+    for r in rows:
+        if r and r[0] == "File Path":
+            path = r[1].split("/")[-1]
+        elif r and r[0] == "Function Name":
+            fn = r[1]
+        elif r and r[0] == "Line No":
+            H = r
+        elif H and r and r[0]:
+            n = r[H.index("# Samples")]
+            out.append((int(n) if n.isdigit() else 0, path, r[0], r[1].strip()))
+    tot = sum(o[0] for o in out) or 1
+    print("# ncu source page, CUDA lines by samples (launch %s: %s): %d samples" % (launch, fn[:70], tot))
+    for n, f, ln, src in sorted(out, reverse=True)[:top]:
+        print("%6.2f%%  %s:%s  %s" % (100 * n / tot, f, ln, src[:110]))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "raw": raw, "source": source}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "raw": raw, "source": source, "lines": lines}[sys.argv[1]](*sys.argv[2:])
