@@ -158,6 +158,10 @@ int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d,
  * hanging the GPU and leaves {tag, blockIdx, threadIdx, parity, ...} here.  out8: 64 uint32 (host): [0,8) first record,
  * [8,64) one word per stuck waiter (tag | warp << 12 | block << 16 | parity << 31). */
 int nerf_debug_tc_watchdog(unsigned int* out8);
+/* wait profile of the CTA-pair kernels (diagnostic; off by default).  on != 0 starts it with zeroed counters, 0 stops it.
+ * out (host, may be NULL) receives the counters accumulated so far: 2 x 512 uint64, [0,512) forward kernel,
+ * [512,1024) dgrad/wgrad kernels; within each, [b] = cycles warps spent waiting on barriers tagged b, [256+b] = waits. */
+int nerf_debug_waitprof(int on, unsigned long long* out);
 
 #ifdef __cplusplus
 }

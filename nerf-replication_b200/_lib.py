@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnerf_b200.so")
+# NERF_B200_LIB selects another build of the same library (the -DNERF_TC_WAITPROF diagnostic flavour); never a fallback
+LIB_PATH = os.environ.get("NERF_B200_LIB") or os.path.join(HERE, "libnerf_b200.so")
 
 NERF_PARAMS_PER_NET = 595844
 NERF_PARAMS_TOTAL = 1191688
@@ -52,6 +53,7 @@ SIGNATURES = {
     "nerf_clip_adam": (_I, [_P, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I, _P]),
     "nerf_debug_umma_probe": (_I, [_I, _P, _P, _P, _I, _I, _I, _P]),
     "nerf_debug_tc_watchdog": (_I, [C.POINTER(C.c_uint)]),
+    "nerf_debug_waitprof": (_I, [_I, C.POINTER(C.c_ulonglong)]),
 }
 
 _lib = None

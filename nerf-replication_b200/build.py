@@ -37,15 +37,23 @@ def up_to_date():
     return os.path.exists(OUT) and os.path.exists(stamp) and open(stamp).read() == _digest()
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, waitprof=False):
+    """waitprof=True builds the diagnostic flavour libnerf_b200_waitprof.so (-DNERF_TC_WAITPROF: every barrier wait of the
+    CTA-pair kernels is timed); select it with NERF_B200_LIB=<path>.  The product library never carries that code."""
+    if waitprof:
+        return _build(OUT.replace(".so", "_waitprof.so"), os.path.join(HERE, "build_waitprof"), ["-DNERF_TC_WAITPROF"], verbose, None)
     if not force and up_to_date():
         return OUT
-    os.makedirs(OBJ, exist_ok=True)
+    return _build(OUT, OBJ, [], verbose, OUT + ".stamp")
+
+
+def _build(out, objdir, extra, verbose, stamp):
+    os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
 
     def compile_one(src):
-        obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        cmd = [nvcc] + NVCC_FLAGS + extra + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))
@@ -55,13 +63,14 @@ def build(force=False, verbose=False):
 
     with concurrent.futures.ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    r = subprocess.run([nvcc, "-shared", "-Wno-deprecated-gpu-targets", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs + ["-lcudart"], capture_output=True, text=True)
+    r = subprocess.run([nvcc, "-shared", "-Wno-deprecated-gpu-targets", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs + ["-lcudart"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
-    with open(OUT + ".stamp", "w") as f:
-        f.write(_digest())
-    return OUT
+    if stamp:
+        with open(stamp, "w") as f:
+            f.write(_digest())
+    return out
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose=True, waitprof="--waitprof" in sys.argv))

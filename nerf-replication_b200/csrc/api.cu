@@ -14,6 +14,8 @@ void tc1_set_debug_sink(unsigned int*);
 void tc2_set_debug_sink(unsigned int*);
 void tc2b_set_debug_sink(unsigned int*);
 void tcp_set_debug_sink(unsigned int*);
+void tc2_set_debug_sink_waitprof(unsigned long long*);
+void tc2b_set_debug_sink_waitprof(unsigned long long*);
 }
 using namespace nerf;
 
@@ -534,6 +536,28 @@ extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* fla
     tc_pack_dgrad_weights(h, flat_param, h->wpack_bwd, (cudaStream_t)stream);
   }
   return post(h, "nerf_clip_adam");
+}
+
+// Wait profile of the CTA-pair kernels (tc_common.cuh waitprof_add).  on != 0: (re)start with zeroed counters; on == 0: stop.
+// out (may be NULL): 2 x 512 uint64 read before the state change -- [0,512) forward TU, [512,1024) backward TU; each
+// [b] = cycles in slow-path waits of tag bucket b = (tag >> 4) & 255, [256 + b] = number of such waits.
+extern "C" int nerf_debug_waitprof(int on, unsigned long long* out) {
+  static unsigned long long* buf = nullptr;
+  cudaDeviceSynchronize();
+  if (out) {
+    if (buf) cudaMemcpy(out, buf, 1024 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    else memset(out, 0, 1024 * sizeof(unsigned long long));
+  }
+  if (on) {
+    if (!buf && cudaMalloc(&buf, 1024 * sizeof(unsigned long long)) != cudaSuccess) return NERF_E_CUDA;
+    cudaMemset(buf, 0, 1024 * sizeof(unsigned long long));
+    nerf::tc2_set_debug_sink_waitprof(buf);
+    nerf::tc2b_set_debug_sink_waitprof(buf + 512);
+  } else {
+    nerf::tc2_set_debug_sink_waitprof(nullptr);
+    nerf::tc2b_set_debug_sink_waitprof(nullptr);
+  }
+  return cudaDeviceSynchronize() == cudaSuccess ? NERF_OK : NERF_E_CUDA;
 }
 
 // watchdog record of the tcgen05 kernels (valid after a trapped launch); out: 8 uint32

@@ -213,7 +213,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
-                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena) {
+                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena, int dbg) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
@@ -327,12 +327,19 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     const bool tile_leader = (q == 0 && lane == 0);
     const uint32_t bar_id = 1 + tile;
     auto before_overwrite = [&]() {
-      if (SAVE) { if (tile_leader) bulk_wait_read0(); named_bar_sync(bar_id, kTile); }
+      if (SAVE) {
+        const long long t0 = waitprof_now();
+        if (tile_leader) { bulk_wait_read0(); waitprof_add(0x900, t0); }
+        named_bar_sync(bar_id, kTile);
+        waitprof_add(0x910, t0);
+      }
     };
     auto save_blocks = [&](uint8_t* tile_base, int slot, const uint8_t* smem_src, int nblocks) {
       if (SAVE) {
+        const long long t0 = waitprof_now();
         named_bar_sync(bar_id, kTile);          // every thread's rows are written and proxy-fenced (signal_ready)
-        if (tile_leader) {
+        waitprof_add(0x920, t0);
+        if (tile_leader && dbg != 1) {
           for (int b = 0; b < nblocks; ++b)
             bulk_s2g(tile_base + (size_t)(slot + b) * arena::kBlockBytes, smem_src + b * 16384, arena::kBlockBytes);
           bulk_commit();
@@ -343,7 +350,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {
       const int64_t g = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
       const bool valid = g < M;
-      uint8_t* tile_base = SAVE ? act_arena + (size_t)(((st * 2 + rank) * 2 + tile)) * arena::act_tile_bytes() : nullptr;
+      uint8_t* tile_base = SAVE ? act_arena + (size_t)(dbg == 2 ? blockIdx.x * 2 + tile : ((st * 2 + rank) * 2 + tile)) * arena::act_tile_bytes() : nullptr;
       float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
       if (valid) row_point(src, g, p, vd);
       before_overwrite();
@@ -405,8 +412,9 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr);
+  static const int dbg = getenv("NERF_DBG_SAVE") ? atoi(getenv("NERF_DBG_SAVE")) : 0;   // timing experiments only
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena, dbg);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr, 0);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));

@@ -226,6 +226,7 @@ struct DgradArgs {
   float* d_t;                       // FINE: [M] += d loss / d t
   const __nv_bfloat16* wpack;       // dgrad stage images of this net
   const float* P;                   // fp32 parameters of this net (heads)
+  int dbg;                           // timing experiments (NERF_DBG_DGRAD): 1 no stores, 2 stores to one tile, 4 masks from one tile
   int64_t M, n_pair;
 };
 
@@ -295,7 +296,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         ++it;
       };
       for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
-        const uint8_t* tb = a.act_arena + (size_t)((st * 2 + rank) * 2 + t) * arena::act_tile_bytes();
+        const uint8_t* tb = a.act_arena + (size_t)((a.dbg & 4) ? blockIdx.x * 2 + t : (st * 2 + rank) * 2 + t) * arena::act_tile_bytes();
         for (int b = 0; b < kInitBlocks; ++b) push(tb + (size_t)(kInitSlot + b) * arena::kBlockBytes);
         for (int i = 0; i < kSteps; ++i) {
           const int ms = step_mask_slot(step_at(i));
@@ -368,7 +369,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     auto save_blocks = [&](uint8_t* gtile, int slot, int nblocks) {
       named_bar_sync(bar_id, kTile);
       if (tile_leader) {
-        for (int b = 0; b < nblocks; ++b) bulk_s2g(gtile + (size_t)(slot + b) * arena::kBlockBytes, sA + b * 16384, arena::kBlockBytes);
+        if (!(a.dbg & 1)) for (int b = 0; b < nblocks; ++b) bulk_s2g(gtile + (size_t)(slot + b) * arena::kBlockBytes, sA + b * 16384, arena::kBlockBytes);
         bulk_commit();
       }
     };
@@ -377,7 +378,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       const int64_t T = (st * 2 + rank) * 2 + tile;
       const int64_t g = T * kTile + row;
       const bool valid = g < a.M;
-      uint8_t* gtile = a.grad_arena + (size_t)T * arena::grad_tile_bytes();
+      uint8_t* gtile = a.grad_arena + (size_t)((a.dbg & 2) ? blockIdx.x * 2 + tile : T) * arena::grad_tile_bytes();
       const float4 dr = valid ? __ldg(a.d_raw + g) : make_float4(0.f, 0.f, 0.f, 0.f);
       float p[3] = {0.f, 0.f, 0.f}, vd[3];
       if (FINE && valid) row_point(a.src, g, p, vd);
@@ -511,6 +512,8 @@ int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const fl
   a.wpack = h->wpack_bwd + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
   a.P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   a.M = M; a.n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
+  static const int dbg = getenv("NERF_DBG_DGRAD") ? atoi(getenv("NERF_DBG_DGRAD")) : 0;   // timing experiments only
+  a.dbg = dbg;
   const int grid = 2 * (int)std::min<int64_t>(a.n_pair, h->num_sms / 2);
   if (full) mlp_tc2_dgrad_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
   else mlp_tc2_dgrad_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
@@ -600,7 +603,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           const uint8_t* xt = at + (size_t)jb.extra_slot * 16384;
           for (int hf = 0; hf < 2; ++hf, ++it) {
             const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
-            mbar_wait(&sb.empty[slot], par ^ 1u, 0x10 + slot);
+            mbar_wait(&sb.empty[slot], par ^ 1u, 0x810 + slot);
             uint8_t* dst = smem + kOffStage + slot * kStageBytes;
             const uint32_t o = hf * kPiece;
             mbar_arrive_expect_tx(&sb.full[slot], (jb.main_slot >= 0 ? 5u : 3u) * kPiece);
@@ -623,7 +626,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         const int t0 = (u / a.n_jobs) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
         for (int k = 2 * (t1 - t0); k > 0; --k, ++it) {
           const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
-          mbar_wait(&sb.full[slot], par, 0x50 + slot);
+          mbar_wait(&sb.full[slot], par, 0x850 + slot);
           mbar_arrive_remote(mapa_u32(smem_u32(&sb.full[slot]), 0));
         }
       }
@@ -637,11 +640,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
         const Job jb = job_of(u % a.n_jobs);
         const int t0 = (u / a.n_jobs) * a.chunk, t1 = min(t0 + a.chunk, a.n_tiles);
-        if (uc > 0) { mbar_wait(&sb.tmem_free, (uc - 1) & 1u, 0x30); tc_fence_after(); }
+        if (uc > 0) { mbar_wait(&sb.tmem_free, (uc - 1) & 1u, 0x830); tc_fence_after(); }
         const uint32_t it0 = it;
         for (int k = 2 * (t1 - t0); k > 0; --k, ++it) {
           const uint32_t slot = it % kStages, par = (it / kStages) & 1u;
-          mbar_wait(&sb.full[slot], par, 0x20 + slot);
+          mbar_wait(&sb.full[slot], par, 0x820 + slot);
           tc_fence_after();
           const uint32_t base = smem_u32(smem + kOffStage + slot * kStageBytes);
 #pragma unroll
@@ -666,7 +669,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     uint32_t uc = 0;
     for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
       const Job jb = job_of(u % a.n_jobs);
-      mbar_wait(&sb.acc_done, uc & 1u, 0x40);
+      mbar_wait(&sb.acc_done, uc & 1u, 0x840);
       tc_fence_after();
       const LayerDim d = layer_dim(jb.layer);
       const int n_base = 128 * (int)rank + q * 32;              // first output row of this warp

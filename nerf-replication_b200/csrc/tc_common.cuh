@@ -17,6 +17,22 @@ static __device__ unsigned int g_tc_debug[8];   // one copy per translation unit
 // optional host-mapped copy (survives the trap that kills the context); set per translation unit by tc_set_debug_sink
 static __device__ unsigned int* g_tc_debug_host = nullptr;
 constexpr long long kWatchdogCycles = 6000000000LL;   // ~3-4 s at B200 clocks
+// wait profile (diagnostic build -DNERF_TC_WAITPROF + nerf_debug_waitprof): [b] = cycles warps spent in barrier waits
+// tagged b = (tag >> 4) & 255, [256 + b] = number of such waits.  Compiled out of the product library.
+static __device__ unsigned long long* g_tc_waitprof = nullptr;
+#ifdef NERF_TC_WAITPROF
+__device__ __forceinline__ long long waitprof_now() { return clock64(); }
+__device__ __forceinline__ void waitprof_add(uint32_t tag, long long t0) {
+  unsigned long long* p = g_tc_waitprof;
+  if (p != nullptr && (__ffs(__activemask()) - 1) == (int)(threadIdx.x & 31)) {
+    atomicAdd(p + ((tag >> 4) & 255u), (unsigned long long)(clock64() - t0));
+    atomicAdd(p + 256 + ((tag >> 4) & 255u), 1ull);
+  }
+}
+#else
+__device__ __forceinline__ long long waitprof_now() { return 0; }
+__device__ __forceinline__ void waitprof_add(uint32_t, long long) {}
+#endif
 
 // ---- mbarrier ---------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -60,17 +76,20 @@ static __device__ __noinline__ void mbar_timeout(uint32_t tag, uint32_t parity) 
   __trap();
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t tag) {
-  if (mbar_try_wait(bar, parity)) return;
+  const long long tp = waitprof_now();
+  if (mbar_try_wait(bar, parity)) { waitprof_add(tag, tp); return; }
   const long long t0 = clock64();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if ((++spins & 0x3FFu) == 0 && clock64() - t0 > kWatchdogCycles) mbar_timeout(tag, parity);
   }
+  waitprof_add(tag, tp);
 }
 
 // host side: point this translation unit's watchdog at a host-mapped buffer
 #define NERF_TC_DEFINE_DEBUG_SINK(fn)                                                              \
-  void fn(unsigned int* mapped) { cudaMemcpyToSymbol(nerf::tc::g_tc_debug_host, &mapped, sizeof(mapped)); }
+  void fn(unsigned int* mapped) { cudaMemcpyToSymbol(nerf::tc::g_tc_debug_host, &mapped, sizeof(mapped)); } \
+  void fn##_waitprof(unsigned long long* buf) { cudaMemcpyToSymbol(nerf::tc::g_tc_waitprof, &buf, sizeof(buf)); }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (UMMA / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

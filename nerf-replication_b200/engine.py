@@ -265,3 +265,13 @@ class Engine:
         out = (C.c_uint * 64)()      # [0..8): first record, [8..64): one word per stuck waiter
         self.lib.nerf_debug_tc_watchdog(out)
         return list(out)
+
+    def waitprof(self, on):
+        """Diagnostic: start (on=True) / stop the barrier wait profile; returns what was accumulated so far as
+        {"fwd"|"bwd": {tag_bucket: (cycles, waits)}} (tag buckets: tc_common.cuh waitprof_add, tag >> 4)."""
+        out = (C.c_ulonglong * 1024)()
+        self._check(self.lib.nerf_debug_waitprof(int(on), out))
+        res = {}
+        for k, name in enumerate(("fwd", "bwd")):
+            res[name] = {b: (out[512 * k + b], out[512 * k + 256 + b]) for b in range(256) if out[512 * k + 256 + b]}
+        return res
