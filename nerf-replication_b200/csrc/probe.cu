@@ -165,8 +165,11 @@ umma_probe2_kernel(const float* __restrict__ A, const float* __restrict__ B, flo
 // (K = reduction dim = "rows").  The operands are staged as [rows x 64-column] 128B-swizzled blocks -- the very
 // images the forward saves -- and described as MN-major: LBO = distance between 64-column blocks, SBO = 1024
 // (8-row groups), one K=16 step = 16 rows = +2048 bytes.
+// layout 0: the 128B-swizzled tile images above.  layout 1/2: un-swizzled "core matrix" images (tc_arena.cuh, half-tile
+// piece): element (row r < 64, column c) at (c/8)*1024 + r*16 + (c%8)*2 -- 8 rows x 8 columns = one contiguous 128-byte
+// core matrix; layout 1 describes it with LBO = 128 (next 8 rows), SBO = 1024 (next 8 columns), layout 2 swaps the two.
 __global__ void __launch_bounds__(128, 1)
-umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt, float* __restrict__ D, int N, int K) {
+umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt, float* __restrict__ D, int N, int K, int layout) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar_done;
@@ -182,11 +185,13 @@ umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt,
   const uint32_t tmem = tmem_base_slot;
   for (int e = tid; e < K * 128; e += 128) {
     const int r = e / 128, c = e % 128;
-    *reinterpret_cast<__nv_bfloat16*>(sA + (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2) = __float2bfloat16(At[e]);
+    const uint32_t off = layout == 0 ? (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2 : (c / 8) * 1024 + r * 16 + (c % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sA + off) = __float2bfloat16(At[e]);
   }
   for (int e = tid; e < K * N; e += 128) {
     const int r = e / N, c = e % N;
-    *reinterpret_cast<__nv_bfloat16*>(sB + (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2) = __float2bfloat16(Bt[e]);
+    const uint32_t off = layout == 0 ? (c / 64) * 16384 + sw128_offset(r, (c % 64) / 8) + (c % 8) * 2 : (c / 8) * 1024 + r * 16 + (c % 8) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(sB + off) = __float2bfloat16(Bt[e]);
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -195,8 +200,15 @@ umma_probe_mn_kernel(const float* __restrict__ At, const float* __restrict__ Bt,
   if (tid == 0) {
     const uint32_t idesc = make_idesc_bf16(128, N, 1, 1);
     for (int ks = 0; ks < K / 16; ++ks) {
-      const uint64_t ad = make_smem_desc(smem_u32(sA) + ks * 2048, 16384, 1024, kLayoutSW128);
-      const uint64_t bd = make_smem_desc(smem_u32(sB) + ks * 2048, 16384, 1024, kLayoutSW128);
+      uint64_t ad, bd;
+      if (layout == 0) {
+        ad = make_smem_desc(smem_u32(sA) + ks * 2048, 16384, 1024, kLayoutSW128);
+        bd = make_smem_desc(smem_u32(sB) + ks * 2048, 16384, 1024, kLayoutSW128);
+      } else {
+        const uint32_t lbo = layout == 1 ? 128 : 1024, sbo = layout == 1 ? 1024 : 128;
+        ad = make_smem_desc(smem_u32(sA) + ks * 256, lbo, sbo, kLayoutNone);
+        bd = make_smem_desc(smem_u32(sB) + ks * 256, lbo, sbo, kLayoutNone);
+      }
       umma_ss(tmem, ad, bd, idesc, ks > 0);
     }
     umma_commit(&bar_done);
@@ -224,11 +236,11 @@ namespace nerf { NERF_TC_DEFINE_DEBUG_SINK(tcp_set_debug_sink) }
 
 extern "C" int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K, void* stream) {
   using namespace nerf;
-  if (variant == 4) {   // a = At [K x 128], b = Bt [K x N]
-    if (M != 128 || N % 64 || N < 64 || N > 256 || K % 16 || K < 16 || K > 128) return NERF_E_INVALID;
+  if (variant >= 4 && variant <= 6) {   // a = At [K x 128], b = Bt [K x N]; 5/6: core-matrix layout, K <= 64
+    if (M != 128 || N % 64 || N < 64 || N > 256 || K % 16 || K < 16 || K > (variant == 4 ? 128 : 64)) return NERF_E_INVALID;
     const size_t smem4 = (size_t)(2 + N / 64) * 16384 + 1024;
     if (cudaFuncSetAttribute(umma_probe_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4) != cudaSuccess) return NERF_E_CUDA;
-    umma_probe_mn_kernel<<<1, 128, smem4, (cudaStream_t)stream>>>(a, b, d, N, K);
+    umma_probe_mn_kernel<<<1, 128, smem4, (cudaStream_t)stream>>>(a, b, d, N, K, variant - 4);
     return cudaGetLastError() == cudaSuccess ? NERF_OK : NERF_E_CUDA;
   }
   if (variant == 3) {

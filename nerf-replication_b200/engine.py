@@ -249,7 +249,7 @@ class Engine:
 
     # -- debug ----------------------------------------------------------------------------------
     def umma_probe(self, variant, a, b):
-        if variant == 4:                       # MN-major operands: a = At [K, 128], b = Bt [K, N]
+        if variant >= 4:                       # MN-major operands: a = At [K, 128], b = Bt [K, N]
             K, M = a.shape
             N = b.shape[1]
         else:

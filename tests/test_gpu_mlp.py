@@ -53,6 +53,22 @@ def test_umma_probe_mn_major(oracle, N, K):
     eng.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,K", [(256, 64), (64, 16), (128, 32)])
+def test_umma_probe_mn_major_core_matrix(oracle, N, K):
+    """MN-major operands in the un-swizzled core-matrix layout of the training arenas (LBO = 128: next 8 rows,
+    SBO = 1024: next 8 columns) -- the form the wgrad kernel consumes."""
+    eng = make_engine(oracle, oracle.init_state_dict(0), "bf16")
+    g = torch.Generator().manual_seed(500 + N + K)
+    at = torch.randn(K, 128, generator=g).bfloat16().float()
+    bt = torch.randn(K, N, generator=g).bfloat16().float()
+    d = eng.umma_probe(5, at.cuda(), bt.cuda())
+    torch.cuda.synchronize()
+    ref = at.double().T @ bt.double()
+    assert maxabs(d, ref) <= 1e-3 * K ** 0.5, eng.watchdog()
+    eng.close()
+
+
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-5)])
 def test_mlp_forward_fp32_golden(oracle, precision, tol):
     g = load_golden("network_forward")
