@@ -92,15 +92,18 @@ constexpr float kInv2PiHi = 0.15915493667125702f;          // fl(1/(2 pi))
 constexpr float kInv2PiLo = 6.4206382432985265e-09f;          // 1/(2 pi) - kInv2PiHi
 
 // Writes one 64-column bf16 K-block row: [v0 v1 v2 | sin(2^k v) cos(2^k v)]_{k<L} | zero pad, 8 columns per 16-byte chunk.
+// grow != nullptr (training forward): the same chunks also go to this row of the block's arena image (tc_arena.cuh).
 template <int L>
-__device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, uint32_t row_xor, const float v[3]) {
+__device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, uint32_t row_xor, const float v[3], uint8_t* grow) {
   float col[8];
   int n = 0, chunk = 0;
   auto push = [&](float x) {
     col[n++] = x;
     if (n == 8) {
-      store_chunk(blk, row_base, row_xor, chunk++, pack_bf16x2(col[0], col[1]), pack_bf16x2(col[2], col[3]),
-                  pack_bf16x2(col[4], col[5]), pack_bf16x2(col[6], col[7]));
+      const uint32_t w0 = pack_bf16x2(col[0], col[1]), w1 = pack_bf16x2(col[2], col[3]);
+      const uint32_t w2 = pack_bf16x2(col[4], col[5]), w3 = pack_bf16x2(col[6], col[7]);
+      if (grow) st_global_cs(grow + chunk * 1024, w0, w1, w2, w3);
+      store_chunk(blk, row_base, row_xor, chunk++, w0, w1, w2, w3);
       n = 0;
     }
   };
@@ -120,10 +123,12 @@ __device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, 
 
 // One 32-column chunk of a trunk-layer epilogue: acc + bias -> (ReLU) -> bf16 -> 4 x 16-byte chunks of the next
 // layer's A operand.  MODE 0: ReLU; 1: ReLU + sigma head accumulation on the fp32 values; 2: linear (feature).
+// grow != nullptr (training forward): the chunk is also stored to this row of the layer's arena blocks, and mbits
+// receives the ReLU bit mask of the 32 columns.
 template <int MODE>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const float* __restrict__ s_bias,
                                           const float* __restrict__ s_walpha, float& sigma, uint8_t* sAct,
-                                          uint32_t row_base, uint32_t row_xor) {
+                                          uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint32_t& mbits) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -147,30 +152,42 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const
   const int ch0 = (c0 & 63) >> 3;
 #pragma unroll
   for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  if (grow) {
+    uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    if (MODE != 2) mbits = pos_bits32(pk);
+  }
 }
 
 // Whole 256-column epilogue of one tile row, TMEM loads software-pipelined against the math of the previous chunk.
+// grow / gmask (training forward): this row of the layer's arena blocks / of its bit-mask record (32 bytes).
 template <int MODE>
 __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_walpha,
-                                          float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor) {
-  uint32_t va[32], vb[32];
+                                          float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor, uint8_t* grow,
+                                          uint8_t* gmask) {
+  uint32_t va[32], vb[32], mw[8];
   tmem_ld32(taddr, va);
 #pragma unroll
   for (int c = 0; c < 8; c += 2) {
     tmem_wait_ld();
     tmem_ld32(taddr + (c + 1) * 32, vb);
-    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor);
+    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, mw[c]);
     tmem_wait_ld();
     if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
-    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor);
+    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, mw[c + 1]);
+  }
+  if (MODE != 2 && gmask) {
+    st_global_cs(gmask, mw[0], mw[1], mw[2], mw[3]);
+    st_global_cs(gmask + 16, mw[4], mw[5], mw[6], mw[7]);
   }
 }
 
 // View-branch epilogue: 128 columns, ReLU, then the 128 -> 3 rgb head on CUDA cores.
 template <bool SAVE>
 __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_wrgb,
-                                          float& r0, float& r1, float& r2, uint8_t* sAct, uint32_t row_base, uint32_t row_xor) {
-  uint32_t va[32], vb[32];
+                                          float& r0, float& r1, float& r2, uint8_t* grow, uint8_t* gmask) {
+  uint32_t va[32], vb[32], mw[4];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
@@ -189,11 +206,11 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       r1 = fmaf(hv[0], w1.x, r1); r1 = fmaf(hv[1], w1.y, r1); r1 = fmaf(hv[2], w1.z, r1); r1 = fmaf(hv[3], w1.w, r1);
       r2 = fmaf(hv[0], w2.x, r2); r2 = fmaf(hv[1], w2.y, r2); r2 = fmaf(hv[2], w2.z, r2); r2 = fmaf(hv[3], w2.w, r2);
     }
-    if (SAVE) {   // keep the hidden view activations (bf16 image in A blocks 0,1) for the backward pass
-      uint8_t* blk = sAct + (c0 >> 6) * 16384;
-      const int ch0 = (c0 & 63) >> 3;
+    if (SAVE) {   // keep the hidden view activations (arena image + bit mask) for the backward pass
+      uint8_t* gb = grow + (c0 >> 6) * 16384 + ((c0 & 63) >> 3) * 1024;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      mw[c0 >> 5] = pos_bits32(pk);
     }
   };
   tmem_ld32(taddr, va);
@@ -206,14 +223,17 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
     if (c + 2 < 4) tmem_ld32(taddr + (c + 2) * 32, va);
     chunk(vb, (c + 1) * 32);
   }
+  if (SAVE) st_global_cs(gmask, mw[0], mw[1], mw[2], mw[3]);
 }
 
-// SAVE: training forward -- every A-operand block (PE, h_0..h_7, feature, PE(dir), view hidden) is also bulk-stored
-// (TMA engine, shared -> global) to the activation arena as it is produced (tc_arena.cuh).
+// SAVE: training forward -- every A-operand block (PE, h_0..h_7, feature, PE(dir), view hidden) is also written to the
+// activation arena straight from the epilogue registers (coalesced st.global.v4 in the arena's core-matrix order,
+// tc_arena.cuh), together with the ReLU bit masks the dgrad chain needs.  (Bulk shared->global stores of the same
+// blocks cost 40 % of the kernel: their shared-memory reads compete with the MMA operand fetch.)
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
-                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena, int dbg) {
+                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
@@ -322,62 +342,38 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
-    // SAVE: the tile's first lane issues the bulk stores; before any in-place overwrite of a stored block it waits
-    // until the TMA engine has finished reading shared memory, then releases the other 127 threads of the tile.
-    const bool tile_leader = (q == 0 && lane == 0);
-    const uint32_t bar_id = 1 + tile;
-    auto before_overwrite = [&]() {
-      if (SAVE) {
-        const long long t0 = waitprof_now();
-        if (tile_leader) { bulk_wait_read0(); waitprof_add(0x900, t0); }
-        named_bar_sync(bar_id, kTile);
-        waitprof_add(0x910, t0);
-      }
-    };
-    auto save_blocks = [&](uint8_t* tile_base, int slot, const uint8_t* smem_src, int nblocks) {
-      if (SAVE) {
-        const long long t0 = waitprof_now();
-        named_bar_sync(bar_id, kTile);          // every thread's rows are written and proxy-fenced (signal_ready)
-        waitprof_add(0x920, t0);
-        if (tile_leader && dbg != 1) {
-          for (int b = 0; b < nblocks; ++b)
-            bulk_s2g(tile_base + (size_t)(slot + b) * arena::kBlockBytes, smem_src + b * 16384, arena::kBlockBytes);
-          bulk_commit();
-        }
-      }
-    };
     uint32_t lc = 0;
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {
       const int64_t g = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
       const bool valid = g < M;
-      uint8_t* tile_base = SAVE ? act_arena + (size_t)(dbg == 2 ? blockIdx.x * 2 + tile : ((st * 2 + rank) * 2 + tile)) * arena::act_tile_bytes() : nullptr;
+      // training forward: this row's slice of the tile's arena blocks / bit-mask records (tc_arena.cuh)
+      uint8_t* tile_base = SAVE ? act_arena + (size_t)((st * 2 + rank) * 2 + tile) * arena::act_tile_bytes() : nullptr;
+      uint8_t* grow0 = SAVE ? tile_base + arena::cm_row_offset(row) : nullptr;
+      uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 32 : nullptr;
+      auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
+      auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
       float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
       if (valid) row_point(src, g, p, vd);
-      before_overwrite();
-      write_pe_block<10>(sPe, row_base, row_xor, p);
+      write_pe_block<10>(sPe, row_base, row_xor, p, gblk(arena::kActPE));
       signal_ready();
-      save_blocks(tile_base, arena::kActPE, sPe, 1);
 
       float sigma = 0.f;
       for (int li = 0; li < kNumSched; ++li, ++lc) {
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
-        before_overwrite();
         const float* bias = s_bias + li * 256;
         if (li < 9) {
-          if (li == 7) epi_layer<1>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
-          else if (li == 8) epi_layer<2>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
-          else epi_layer<0>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor);
+          uint8_t* grow = gblk(li < 8 ? arena::kActH + 4 * li : arena::kActFeat);
+          if (li == 7) epi_layer<1>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
+          else if (li == 8) epi_layer<2>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr);
+          else epi_layer<0>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
-          if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd);
+          if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd, gblk(arena::kActPEDir));
           signal_ready();
-          save_blocks(tile_base, li < 8 ? arena::kActH + 4 * li : arena::kActFeat, sAct, 4);
-          if (SAVE && li == 5 && tile_leader) { bulk_s2g(tile_base + (size_t)arena::kActPEDir * arena::kBlockBytes, sPe, arena::kBlockBytes); bulk_commit(); }
         } else {
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-          epi_views<SAVE>(taddr, bias, s_wrgb, r0, r1, r2, sAct, row_base, row_xor);
+          epi_views<SAVE>(taddr, bias, s_wrgb, r0, r1, r2, gblk(arena::kActHV), gmsk(arena::kMaskHV));
           tc_fence_before();
-          if (SAVE) { fence_proxy_async_smem(); save_blocks(tile_base, arena::kActHV, sAct, 2); }
           if (valid) {
             float4 o = make_float4(r0 + __ldg(P + b_off(L_RGB)), r1 + __ldg(P + b_off(L_RGB) + 1), r2 + __ldg(P + b_off(L_RGB) + 2),
                                    sigma + __ldg(P + b_off(L_ALPHA)));
@@ -387,7 +383,6 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
         }
       }
     }
-    if (SAVE && tile_leader) bulk_wait0();       // outstanding bulk stores must complete before the CTA may exit
   }
   tc_fence_before();
   cluster_sync_all();
@@ -412,9 +407,8 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
-  static const int dbg = getenv("NERF_DBG_SAVE") ? atoi(getenv("NERF_DBG_SAVE")) : 0;   // timing experiments only
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena, dbg);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr, 0);
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));

@@ -3,9 +3,9 @@
 //   dgrad chain  (this file, part 1): per 128-row tile the whole chain  d raw -> d hv -> d feature -> dZ7 ... dZ0
 //                (-> d PE -> d t for the fine net) runs inside one persistent CTA-pair kernel; the gradient tile
 //                stays in shared memory as the A operand of the next tcgen05.mma (M=256, cta_group::2), transposed
-//                weight stage images stream through a 3-deep ring, the ReLU masks come from the activation images
-//                the forward saved (streamed through a second ring), and every dZ_l tile is bulk-stored to the
-//                gradient arena for the weight-gradient kernel.
+//                weight stage images stream through a 6-deep ring, the ReLU masks are the bit masks the forward
+//                saved (32 bytes per row and layer, loaded into registers ahead of the accumulator wait), and every
+//                dZ_l tile is written to the gradient arena straight from the epilogue registers.
 //   wgrad        (part 2): dW_l = dZ_l^T X_{l-1} summed over all rows -- the saved tile images are used directly as
 //                MN-major operands (reduction dimension = rows), accumulators [256 x 384] fp32 in TMEM across a CTA
 //                pair, one red.global.add flush per (layer, tile range) work unit.
@@ -28,9 +28,7 @@ constexpr int kTile = 128;
 constexpr int kRowsPerCta = 256, kRowsPerPair = 512;
 constexpr int kStageImage = 32768;
 constexpr int kHalfBytes = 16384;
-constexpr int kRing = 2;        // weight stages in flight
-constexpr int kMaskRing = 2;    // mask blocks in flight PER TILE (each tile has its own ring and producer lane: a shared ring
-                                // lets the later tile wait more than one ring cycle ahead, where parity waits alias)
+constexpr int kRing = 6;        // weight stages in flight
 constexpr int kThreads = 384;
 constexpr int kNumSteps = 11;      // V1, F, L7, L6, PE5, L5, L4, L3, L2, L1, P0
 constexpr int kNumStages = 42;
@@ -51,11 +49,10 @@ __host__ __device__ constexpr int step_layer(int s) {
 }
 __host__ __device__ constexpr int step_col0(int s) { return s == S_L5 ? 63 : 0; }
 __host__ __device__ constexpr int step_ncols(int s) { return (s == S_PE5 || s == S_P0) ? 63 : 256; }
-// activation-arena slot of the ReLU mask the step's epilogue applies (-1: none) and gradient-arena slot it writes
-__host__ __device__ constexpr int step_mask_slot(int s) {
-  return s == S_F ? arena::kActH + 28 : s == S_L7 ? arena::kActH + 24 : s == S_L6 ? arena::kActH + 20
-       : s == S_L5 ? arena::kActH + 16 : s == S_L4 ? arena::kActH + 12 : s == S_L3 ? arena::kActH + 8
-       : s == S_L2 ? arena::kActH + 4 : s == S_L1 ? arena::kActH + 0 : -1;
+// trunk layer whose ReLU bit mask the step's epilogue applies (-1: none) and gradient-arena slot it writes
+__host__ __device__ constexpr int step_mask_layer(int s) {
+  return s == S_F ? 7 : s == S_L7 ? 6 : s == S_L6 ? 5 : s == S_L5 ? 4 : s == S_L4 ? 3 : s == S_L3 ? 2 : s == S_L2 ? 1
+       : s == S_L1 ? 0 : -1;
 }
 __host__ __device__ constexpr int step_out_slot(int s) {
   return s == S_V1 ? arena::kGradFeat : s == S_F ? arena::kGradZ + 28 : s == S_L7 ? arena::kGradZ + 24
@@ -64,13 +61,13 @@ __host__ __device__ constexpr int step_out_slot(int s) {
 }
 
 // shared memory map
-constexpr uint32_t kOffA = 0, kOffW = 131072, kOffMask = kOffW + kRing * kHalfBytes;      // 180224
-constexpr uint32_t kOffHeads = kOffMask + 2 * kMaskRing * 16384;                                // 229376: w_alpha[256] | w_rgb[384]
+constexpr uint32_t kOffA = 0, kOffW = 131072;
+constexpr uint32_t kOffHeads = kOffW + kRing * kHalfBytes;                                  // 229376: w_alpha[256] | w_rgb[384]
 constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;                                   // 231936
 constexpr uint32_t kSmemBytes = kOffBar + 256;                                              // 232192 <= 232448
 
 struct Bars {
-  uint64_t w_full[kRing], w_empty[kRing], m_full[2][kMaskRing], m_empty[2][kMaskRing], acc_full[2], act_ready[2];
+  uint64_t w_full[kRing], w_empty[kRing], acc_full[2], act_ready[2];
   uint32_t tmem_slot;
 };
 static_assert(sizeof(Bars) <= 256, "barrier block");
@@ -112,16 +109,6 @@ __device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uin
                                             uint32_t b, uint32_t c, uint32_t d) {
   *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
 }
-__device__ __forceinline__ uint4 load_chunk(const uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk) {
-  return *reinterpret_cast<const uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4));
-}
-// per-half "h > 0" mask of a post-ReLU bf16x2 word: 0xFFFF where the half is positive (HSET2.BF16)
-__device__ __forceinline__ uint32_t relu_mask2(uint32_t h) {
-  uint32_t d, z = 0;
-  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(z));
-  return d;
-}
-
 constexpr float kInv2PiHi = 0.15915493667125702f, kInv2PiLo = 6.4206382432985265e-09f;
 __device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, float& s, float& c) {
   const float r = x * c_hi;
@@ -133,53 +120,37 @@ __device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, fl
   c = __cosf(ang);
 }
 
-// The per-tile consumer view of its mask ring: blocks are produced (one producer lane per tile) and consumed by
-// the tile's 4 warps in one order: [init blocks] then, for every masked step, 4 blocks.
-struct MaskRing {
-  uint64_t* full;      // m_full[tile]
-  uint64_t* empty;     // m_empty[tile]
-  uint8_t* base;       // this tile's ring memory
-  uint32_t next;       // index of the next block of this tile
-  int lane;
-  __device__ __forceinline__ const uint8_t* acquire(uint32_t idx) {
-    mbar_wait(&full[idx % kMaskRing], (idx / kMaskRing) & 1u, 0x600 + (idx & 0xff));
-    return base + (idx % kMaskRing) * 16384;
-  }
-  __device__ __forceinline__ void release(uint32_t idx) {     // one arrive per warp (m_empty counts 4)
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[idx % kMaskRing]);
-  }
-};
+// 16 packed words (32 columns) -> shared-memory A operand (swizzled) + this row of the gradient arena block
+__device__ __forceinline__ void put_chunk(const uint32_t (&pk)[16], int c0, uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
+  uint8_t* blk = sA + (c0 >> 6) * 16384;
+  const int ch0 = (c0 & 63) >> 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+}
 
 // Epilogue of a masked step (F, L7..L1): 256 accumulator columns -> (+ d_sigma * w_alpha for F) -> bf16 -> AND
-// with the ReLU mask of the saved activation -> next A operand (in place).
+// with the saved ReLU bit mask (mw: 8 words of this row) -> next A operand (in place) + gradient arena.
 template <bool ADD_ALPHA>
-__device__ __forceinline__ void epi_masked(uint32_t taddr, MaskRing& mr, uint32_t first_idx, float dsigma,
-                                           const float* __restrict__ s_walpha, uint8_t* sA, uint32_t row_base, uint32_t row_xor) {
+__device__ __forceinline__ void epi_masked(uint32_t taddr, const uint32_t (&mw)[8], float dsigma, const float* __restrict__ s_walpha,
+                                           uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint32_t va[32], vb[32];
-  const uint8_t* hb = nullptr;
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
-    if ((c0 & 63) == 0) hb = mr.acquire(first_idx + (c0 >> 6));
+    const uint32_t bits = mw[c0 >> 5];
     uint32_t pk[16];
 #pragma unroll
-    for (int q4 = 0; q4 < 4; ++q4) {
-      const uint4 hw = load_chunk(hb, row_base, row_xor, ((c0 & 63) >> 3) + q4);
-      const uint32_t hws[4] = {hw.x, hw.y, hw.z, hw.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float f0 = __uint_as_float(v[8 * q4 + 2 * j]), f1 = __uint_as_float(v[8 * q4 + 2 * j + 1]);
-        if (ADD_ALPHA) {
-          f0 = fmaf(dsigma, s_walpha[c0 + 8 * q4 + 2 * j], f0);
-          f1 = fmaf(dsigma, s_walpha[c0 + 8 * q4 + 2 * j + 1], f1);
-        }
-        pk[4 * q4 + j] = pack_bf16x2(f0, f1) & relu_mask2(hws[j]);
+    for (int i = 0; i < 16; ++i) {
+      float f0 = __uint_as_float(v[2 * i]), f1 = __uint_as_float(v[2 * i + 1]);
+      if (ADD_ALPHA) {
+        const float2 wa = *reinterpret_cast<const float2*>(s_walpha + c0 + 2 * i);
+        f0 = fmaf(dsigma, wa.x, f0);
+        f1 = fmaf(dsigma, wa.y, f1);
       }
+      pk[i] = pack_bf16x2(f0, f1) & mask2_from_bits(bits, i);
     }
-    uint8_t* blk = sA + (c0 >> 6) * 16384;
-    const int ch0 = (c0 & 63) >> 3;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-    if ((c0 & 63) == 32) mr.release(first_idx + (c0 >> 6));
+    put_chunk(pk, c0, sA, row_base, row_xor, grow);
   };
   tmem_ld32(taddr, va);
 #pragma unroll
@@ -193,17 +164,14 @@ __device__ __forceinline__ void epi_masked(uint32_t taddr, MaskRing& mr, uint32_
   }
 }
 
-// Epilogue of the linear step V1 (d feature): 256 columns -> bf16 -> A operand.
-__device__ __forceinline__ void epi_linear(uint32_t taddr, uint8_t* sA, uint32_t row_base, uint32_t row_xor) {
+// Epilogue of the linear step V1 (d feature): 256 columns -> bf16 -> A operand + gradient arena.
+__device__ __forceinline__ void epi_linear(uint32_t taddr, uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint32_t va[32], vb[32];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-    uint8_t* blk = sA + (c0 >> 6) * 16384;
-    const int ch0 = (c0 & 63) >> 3;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    put_chunk(pk, c0, sA, row_base, row_xor, grow);
   };
   tmem_ld32(taddr, va);
 #pragma unroll
@@ -226,7 +194,6 @@ struct DgradArgs {
   float* d_t;                       // FINE: [M] += d loss / d t
   const __nv_bfloat16* wpack;       // dgrad stage images of this net
   const float* P;                   // fp32 parameters of this net (heads)
-  int dbg;                           // timing experiments (NERF_DBG_DGRAD): 1 no stores, 2 stores to one tile, 4 masks from one tile
   int64_t M, n_pair;
 };
 
@@ -245,13 +212,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   constexpr int kCoarseSteps[7] = {S_L7, S_L6, S_L5, S_L4, S_L3, S_L2, S_L1};
   auto step_at = [&](int i) { return FINE ? kFineSteps[i] : kCoarseSteps[i]; };
   constexpr int kInitBlocks = FINE ? 2 : 4;                                   // hv (2 blocks) / h7 (4 blocks)
-  constexpr int kInitSlot = FINE ? arena::kActHV : arena::kActH + 28;
+  constexpr int kInitMask = FINE ? arena::kMaskHV : arena::kMaskH + 7;
 
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA13, smem_u32(smem));
   if (tid == 0) {
     for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
-    for (int t = 0; t < 2; ++t)
-      for (int i = 0; i < kMaskRing; ++i) { mbar_init(&sb.m_full[t][i], 1); mbar_init(&sb.m_empty[t][i], 4); }
     for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
     fence_barrier_init();
   }
@@ -281,29 +246,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
                      bytes, &sb.w_full[slot]);
           }
         }
-    }
-    __syncwarp();
-  } else if (warp == 2 || warp == 3) {
-    // ===== mask producers: warp 2 feeds tile X's ring, warp 3 tile Y's, saved activation blocks in consumption order =====
-    if (lane == 0) {
-      const int t = warp - 2;
-      uint32_t it = 0;
-      auto push = [&](const uint8_t* src_block) {
-        const uint32_t slot = it % kMaskRing, par = (it / kMaskRing) & 1u;
-        mbar_wait(&sb.m_empty[t][slot], par ^ 1u, 0x700 + (it & 0xff));
-        mbar_arrive_expect_tx(&sb.m_full[t][slot], 16384u);
-        bulk_g2s(smem + kOffMask + (t * kMaskRing + slot) * 16384, src_block, 16384u, &sb.m_full[t][slot]);
-        ++it;
-      };
-      for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
-        const uint8_t* tb = a.act_arena + (size_t)((a.dbg & 4) ? blockIdx.x * 2 + t : (st * 2 + rank) * 2 + t) * arena::act_tile_bytes();
-        for (int b = 0; b < kInitBlocks; ++b) push(tb + (size_t)(kInitSlot + b) * arena::kBlockBytes);
-        for (int i = 0; i < kSteps; ++i) {
-          const int ms = step_mask_slot(step_at(i));
-          if (ms < 0) continue;
-          for (int b = 0; b < 4; ++b) push(tb + (size_t)(ms + b) * arena::kBlockBytes);
-        }
-      }
     }
     __syncwarp();
   } else if (warp == 1 && rank == 1) {
@@ -356,67 +298,58 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     uint8_t* sA = smem + kOffA + tile * 65536;
     const uint32_t row_base = (uint32_t)((row >> 3) * 1024 + (row & 7) * 128), row_xor = (uint32_t)(row & 7);
     const uint32_t ready_addr = mapa_u32(smem_u32(&sb.act_ready[tile]), 0);
-    const bool tile_leader = (q == 0 && lane == 0);
-    const uint32_t bar_id = 1 + tile;
-    MaskRing mr{sb.m_full[tile], sb.m_empty[tile], smem + kOffMask + tile * kMaskRing * 16384, 0u, lane};
     auto signal_ready = [&]() {
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
-    auto before_overwrite = [&]() { if (tile_leader) bulk_wait_read0(); named_bar_sync(bar_id, kTile); };
-    auto save_blocks = [&](uint8_t* gtile, int slot, int nblocks) {
-      named_bar_sync(bar_id, kTile);
-      if (tile_leader) {
-        if (!(a.dbg & 1)) for (int b = 0; b < nblocks; ++b) bulk_s2g(gtile + (size_t)(slot + b) * arena::kBlockBytes, sA + b * 16384, arena::kBlockBytes);
-        bulk_commit();
-      }
-    };
     uint32_t lc = 0;
     for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
       const int64_t T = (st * 2 + rank) * 2 + tile;
       const int64_t g = T * kTile + row;
       const bool valid = g < a.M;
-      uint8_t* gtile = a.grad_arena + (size_t)((a.dbg & 2) ? blockIdx.x * 2 + tile : T) * arena::grad_tile_bytes();
+      // this row's slice of the tile's gradient-arena blocks and of its saved ReLU bit masks
+      uint8_t* grow0 = a.grad_arena + (size_t)T * arena::grad_tile_bytes() + arena::cm_row_offset(row);
+      const uint8_t* mrow0 = a.act_arena + (size_t)T * arena::act_tile_bytes() + arena::act_mask_offset() + row * 32;
+      auto load_mask = [&](int layer, uint32_t (&mw)[8]) {
+        const uint4* mp = reinterpret_cast<const uint4*>(mrow0 + layer * arena::kMaskLayerBytes);
+        const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+        mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+      };
       const float4 dr = valid ? __ldg(a.d_raw + g) : make_float4(0.f, 0.f, 0.f, 0.f);
       float p[3] = {0.f, 0.f, 0.f}, vd[3];
       if (FINE && valid) row_point(a.src, g, p, vd);
 
       // ---- init: the first A operand from d raw ----
-      before_overwrite();
       {
-        const uint32_t first = mr.next;
-        for (int b = 0; b < kInitBlocks; ++b) {
-          const uint8_t* hb = mr.acquire(first + b);
+        uint32_t mw[8];
+        load_mask(kInitMask, mw);
+        uint8_t* grow = grow0 + (size_t)(FINE ? arena::kGradHV : arena::kGradZ + 28) * arena::kBlockBytes;
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const uint4 hw = load_chunk(hb, row_base, row_xor, ch);
-            const uint32_t hws[4] = {hw.x, hw.y, hw.z, hw.w};
-            uint32_t pk[4];
+        for (int c32 = 0; c32 < 2 * kInitBlocks; ++c32) {
+          uint32_t pk[16];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int c = b * 64 + ch * 8 + 2 * j;
-              float f0, f1;
-              if (FINE) {      // d hv_pre = W_rgb^T d rgb, masked by hv > 0   (rgb_linear.weight [3,128])
-                f0 = dr.x * s_wrgb[c] + dr.y * s_wrgb[128 + c] + dr.z * s_wrgb[256 + c];
-                f1 = dr.x * s_wrgb[c + 1] + dr.y * s_wrgb[128 + c + 1] + dr.z * s_wrgb[256 + c + 1];
-              } else {         // d h7 = w_alpha d sigma, masked by h7 > 0
-                f0 = dr.w * s_walpha[c]; f1 = dr.w * s_walpha[c + 1];
-              }
-              pk[j] = pack_bf16x2(f0, f1) & relu_mask2(hws[j]);
+          for (int i = 0; i < 16; ++i) {
+            const int c = c32 * 32 + 2 * i;
+            float f0, f1;
+            if (FINE) {      // d hv_pre = W_rgb^T d rgb, masked by hv > 0   (rgb_linear.weight [3,128])
+              f0 = dr.x * s_wrgb[c] + dr.y * s_wrgb[128 + c] + dr.z * s_wrgb[256 + c];
+              f1 = dr.x * s_wrgb[c + 1] + dr.y * s_wrgb[128 + c + 1] + dr.z * s_wrgb[256 + c + 1];
+            } else {         // d h7 = w_alpha d sigma, masked by h7 > 0
+              f0 = dr.w * s_walpha[c]; f1 = dr.w * s_walpha[c + 1];
             }
-            store_chunk(sA + b * 16384, row_base, row_xor, ch, pk[0], pk[1], pk[2], pk[3]);
+            pk[i] = pack_bf16x2(f0, f1) & mask2_from_bits(mw[c32], i);
           }
-          mr.release(first + b);
+          put_chunk(pk, c32 * 32, sA, row_base, row_xor, grow);
         }
-        mr.next += kInitBlocks;
       }
       signal_ready();
-      save_blocks(gtile, FINE ? arena::kGradHV : arena::kGradZ + 28, kInitBlocks);
 
       for (int i = 0; i < kSteps; ++i, ++lc) {
         const int s = step_at(i);
+        uint32_t mw_next[8];
+        if (step_mask_layer(s) >= 0) load_mask(step_mask_layer(s), mw_next);     // in flight while the MMAs finish
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
         if (s == S_PE5) {
@@ -469,20 +402,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             a.d_t[g] += acc;
           }
         } else {
-          before_overwrite();
-          if (s == S_V1) epi_linear(taddr, sA, row_base, row_xor);
-          else {
-            const uint32_t first = mr.next;
-            if (s == S_F) epi_masked<true>(taddr, mr, first, dr.w, s_walpha, sA, row_base, row_xor);
-            else epi_masked<false>(taddr, mr, first, 0.f, s_walpha, sA, row_base, row_xor);
-            mr.next += 4;
-          }
-          if (i + 1 < kSteps) signal_ready(); else { fence_proxy_async_smem(); tc_fence_before(); }
-          save_blocks(gtile, step_out_slot(s), 4);
+          uint8_t* grow = grow0 + (size_t)step_out_slot(s) * arena::kBlockBytes;
+          if (s == S_V1) epi_linear(taddr, sA, row_base, row_xor, grow);
+          else if (s == S_F) epi_masked<true>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
+          else epi_masked<false>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
+          if (i + 1 < kSteps) signal_ready(); else tc_fence_before();
         }
       }
     }
-    if (tile_leader) bulk_wait0();
   }
   tc_fence_before();
   cluster_sync_all();
@@ -512,8 +439,6 @@ int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const fl
   a.wpack = h->wpack_bwd + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
   a.P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   a.M = M; a.n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
-  static const int dbg = getenv("NERF_DBG_DGRAD") ? atoi(getenv("NERF_DBG_DGRAD")) : 0;   // timing experiments only
-  a.dbg = dbg;
   const int grid = 2 * (int)std::min<int64_t>(a.n_pair, h->num_sms / 2);
   if (full) mlp_tc2_dgrad_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
   else mlp_tc2_dgrad_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
@@ -648,12 +573,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           tc_fence_after();
           const uint32_t base = smem_u32(smem + kOffStage + slot * kStageBytes);
 #pragma unroll
+          // core-matrix pieces (tc_arena.cuh) as MN-major operands: LBO = 128 (next 8 rows), SBO = 1024 (next 8 columns;
+          // consecutive pieces continue the column index: 8 KB = 8 x SBO), one K = 16 step = 256 bytes
           for (int ks = 0; ks < kHalfRows / 16; ++ks) {
             const uint32_t acc = (it > it0 || ks > 0) ? 1u : 0u;
-            const uint64_t ad = make_smem_desc(base + ks * 2048, kPiece, 1024, kLayoutSW128);
+            const uint64_t ad = make_smem_desc(base + ks * 256, 128, 1024, kLayoutNone);
             if (jb.main_slot >= 0)
-              umma_ss2(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 2048, kPiece, 1024, kLayoutSW128), idesc_main, acc);
-            umma_ss2(tmem + 256, ad, make_smem_desc(base + 4 * kPiece + ks * 2048, kPiece, 1024, kLayoutSW128), idesc_extra, acc);
+              umma_ss2(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_main, acc);
+            umma_ss2(tmem + 256, ad, make_smem_desc(base + 4 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_extra, acc);
           }
           umma_commit2(&sb.empty[slot], 0x3);
         }
@@ -709,8 +636,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 }
 
 // Heads on CUDA cores: alpha_linear (d sigma^T h7) and rgb_linear (d rgb^T hv) + their biases, straight from the
-// saved tile images.  Warp w streams head block w of every tile of its CTA (0..3: h7, 4..5: hv); a lane owns one
-// logical 16-byte chunk (8 columns) of every fourth row, so a warp instruction reads four whole 128-byte rows.
+// saved arena blocks.  Warp w streams head block w of every tile of its CTA (0..3: h7, 4..5: hv); a lane owns one
+// 16-byte chunk (8 columns) of every fourth row, so a warp instruction reads 8 runs of 64 contiguous bytes.
 __global__ void __launch_bounds__(192) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
                                                           int64_t M, int n_tiles, int fine, float* __restrict__ G) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -729,7 +656,7 @@ __global__ void __launch_bounds__(192) wgrad_heads_kernel(const uint8_t* __restr
 #pragma unroll 8
     for (int i = 0; i < 32; ++i) {
       const int r = 4 * i + rs;
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(blk + sw128_offset(r, j)));
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(blk + arena::cm_row_offset(r) + j * 1024));
       const float4 dr = g0 + r < M ? __ldg(d_raw + g0 + r) : make_float4(0.f, 0.f, 0.f, 0.f);
       const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll

@@ -1,9 +1,16 @@
 // tc_arena.cuh -- layout of the training arenas shared by the tensor-core forward (save), dgrad and wgrad kernels.
 //
-// Everything a training step keeps between kernels is stored as "tile images": one 16 KB block = 128 rows x 64
-// bf16 columns, K-major with the 128-byte swizzle -- byte for byte what a tcgen05 shared-memory operand looks
-// like.  The same image is a K-major operand [rows x cols] (forward / dgrad: A = activations) and an MN-major
-// operand [cols x rows] (wgrad: dW = dZ^T X reduces over rows), so no kernel ever transposes or re-tiles.
+// Everything a training step keeps between kernels is stored as 16 KB blocks of 128 rows x 64 bf16 columns in
+// the un-swizzled tcgen05 "core matrix" order, split in two 64-row halves:
+//     byte offset of (row r, column c) = (r / 64) * 8192 + (c / 8) * 1024 + (r % 64) * 16 + (c % 8) * 2
+// i.e. 8 rows x 8 columns form one contiguous 128-byte core matrix.  Two properties make this the layout:
+//   * the producer kernels hold one row per thread (TMEM lane) and 8 consecutive columns per 16-byte register
+//     quad, so a warp's st.global.v4 covers 32 rows x 16 B = 512 contiguous bytes: the images are written
+//     straight from registers, fully coalesced, without a second pass through shared memory;
+//   * wgrad (dW = dZ^T X, reduction over rows) bulk-copies half-block pieces (8 KB, contiguous) into shared
+//     memory and uses them as MN-major operands: descriptor LBO = 128 (next 8 rows), SBO = 1024 (next 8
+//     columns), one K = 16 step = +256 bytes -- no kernel ever transposes or re-tiles.
+// The ReLU masks the dgrad chain needs are kept separately as bits (32 B per row and layer instead of 512 B).
 //
 // Tile T = ((pair_super_tile * 2 + cta_rank) * 2 + xy) covers rows [T*128, T*128+128) of the MLP row space
 // (row g = ray * S + sample), identical in all three kernels.
@@ -21,13 +28,22 @@ constexpr int kActFeat = 33;     // feature_linear output (linear), 4 blocks
 constexpr int kActPEDir = 37;    // PE(dir): 27 values, column 63 = 1.0
 constexpr int kActHV = 38;       // views hidden (post-ReLU), 2 blocks
 constexpr int kActBlocks = 40;
+// ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][row 0..127][8 x uint32]
+//      word w of a row covers columns [32 w, 32 w + 32): bit i = column 32 w + 2 i, bit 16 + i = column 32 w + 2 i + 1
+constexpr int kMaskH = 0;        // h_l > 0, l = 0..7
+constexpr int kMaskHV = 8;       // views hidden > 0 (words 0..3)
+constexpr int kMaskLayers = 9;
+constexpr int kMaskLayerBytes = 128 * 32;
 // ---- gradient arena (written by the dgrad chain) : block slots per tile
 constexpr int kGradZ = 0;        // dZ_l (grad wrt pre-activation of trunk layer l), l = 0..7 : slots 4 l + b
 constexpr int kGradFeat = 32;    // grad wrt feature_linear output, 4 blocks
 constexpr int kGradHV = 36;      // grad wrt views pre-activation, 2 blocks
 constexpr int kGradBlocks = 38;
 
-__host__ __device__ constexpr size_t act_tile_bytes() { return (size_t)kActBlocks * kBlockBytes; }
+__host__ __device__ constexpr size_t act_mask_offset() { return (size_t)kActBlocks * kBlockBytes; }
+__host__ __device__ constexpr size_t act_tile_bytes() { return act_mask_offset() + (size_t)kMaskLayers * kMaskLayerBytes; }
+// offset of a row's first 16-byte chunk inside a block; chunk c8 (8 columns) adds c8 * 1024
+__host__ __device__ constexpr uint32_t cm_row_offset(int row) { return (uint32_t)((row >> 6) * 8192 + (row & 63) * 16); }
 __host__ __device__ constexpr size_t grad_tile_bytes() { return (size_t)kGradBlocks * kBlockBytes; }
 // number of 128-row tiles the pair-tiled kernels touch for M rows
 __host__ __device__ constexpr int64_t num_tiles(int64_t M) { return ((M + 511) / 512) * 4; }

@@ -195,6 +195,26 @@ __host__ __device__ __forceinline__ uint32_t sw128_offset(int row, int chunk16 /
   return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk16 ^ (row & 7)) << 4));
 }
 
+// per-half "x > 0" mask of a bf16x2 word: 0xFFFF where the half is positive (HSET2.BF16)
+__device__ __forceinline__ uint32_t pos_mask2(uint32_t h) {
+  uint32_t d, z = 0;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(z));
+  return d;
+}
+// 16 bf16x2 words (32 columns) -> one mask word: bit i = low half of word i positive, bit 16 + i = high half (tc_arena.cuh)
+__device__ __forceinline__ uint32_t pos_bits32(const uint32_t (&pk)[16]) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) m |= pos_mask2(pk[i]) & (0x00010001u << i);
+  return m;
+}
+// inverse for one word: 0xFFFF in the halves whose bits (i, 16 + i) are set
+__device__ __forceinline__ uint32_t mask2_from_bits(uint32_t bits, int i) { return ((bits >> i) & 0x00010001u) * 0xFFFFu; }
+// streaming 16-byte global store (written once, read by a later kernel after far more than L2-size traffic)
+__device__ __forceinline__ void st_global_cs(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   uint32_t r;
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
