@@ -14,10 +14,10 @@
 //   warp 1      rank 0: MMA issuer -- one lane issues tcgen05.mma.cta_group::2 (M=256, N=256|128, K=16) for X
 //               then Y on every stage; tcgen05.commit multicast to both CTAs' barriers
 //               rank 1: forwarder -- relays "my half of the stage has landed" to the leader's barrier
-//   warp 2      TMEM allocator (cta_group::2, 512 columns: X accumulators [0,256), Y [256,512))
-//   warps 4-7   tile X: positional encoding -> bf16 A operand; per layer TMEM -> +bias (shared memory), ReLU ->
+//               both: TMEM allocation (cta_group::2, 512 columns: X accumulators [0,256), Y [256,512))
+//   warps 2-5   tile X: positional encoding -> bf16 A operand; per layer TMEM -> +bias (shared memory), ReLU ->
 //               bf16 -> A operand of the next layer (in place); sigma / rgb heads on CUDA cores
-//   warps 8-11  same for tile Y
+//   warps 6-9   same for tile Y
 // Shared memory (bytes): A_X 64K | A_Y 64K | PE_X 16K | PE_Y 16K | W ring 3 x 16K | biases 9.5K | heads 2.5K | barriers
 #include "engine.h"
 #include "tc_common.cuh"
@@ -37,7 +37,7 @@ constexpr int kHalfBytes = 16384;               // this CTA's half of a 256-row 
 constexpr int kRing = 3;
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
 constexpr int kNumStages = 39;
-constexpr int kThreads = 384;
+constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
 constexpr int kBiasFloats = kNumSched * 256;    // bias of schedule entry li at [li*256, +N)
 constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
 constexpr uint32_t kOffBias = kOffW + kRing * kHalfBytes;         // 212992
@@ -128,7 +128,7 @@ __device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, 
 template <int MODE>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const float* __restrict__ s_bias,
                                           const float* __restrict__ s_walpha, float& sigma, uint8_t* sAct,
-                                          uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint32_t& mbits) {
+                                          uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint8_t* gmask) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -156,30 +156,26 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const
     uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
     for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-    if (MODE != 2) mbits = pos_bits32(pk);
+    if (MODE != 2) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
   }
 }
 
 // Whole 256-column epilogue of one tile row, TMEM loads software-pipelined against the math of the previous chunk.
-// grow / gmask (training forward): this row of the layer's arena blocks / of its bit-mask record (32 bytes).
+// grow / gmask (training forward): this row of the layer's arena blocks / of its bit-mask record.
 template <int MODE>
 __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_walpha,
                                           float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor, uint8_t* grow,
                                           uint8_t* gmask) {
-  uint32_t va[32], vb[32], mw[8];
+  uint32_t va[32], vb[32];
   tmem_ld32(taddr, va);
 #pragma unroll
   for (int c = 0; c < 8; c += 2) {
     tmem_wait_ld();
     tmem_ld32(taddr + (c + 1) * 32, vb);
-    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, mw[c]);
+    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
     tmem_wait_ld();
     if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
-    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, mw[c + 1]);
-  }
-  if (MODE != 2 && gmask) {
-    st_global_cs(gmask, mw[0], mw[1], mw[2], mw[3]);
-    st_global_cs(gmask + 16, mw[4], mw[5], mw[6], mw[7]);
+    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
   }
 }
 
@@ -187,7 +183,7 @@ __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restric
 template <bool SAVE>
 __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_wrgb,
                                           float& r0, float& r1, float& r2, uint8_t* grow, uint8_t* gmask) {
-  uint32_t va[32], vb[32], mw[4];
+  uint32_t va[32], vb[32];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
@@ -210,7 +206,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       uint8_t* gb = grow + (c0 >> 6) * 16384 + ((c0 & 63) >> 3) * 1024;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      mw[c0 >> 5] = pos_bits32(pk);
+      *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
     }
   };
   tmem_ld32(taddr, va);
@@ -223,7 +219,6 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
     if (c + 2 < 4) tmem_ld32(taddr + (c + 2) * 32, va);
     chunk(vb, (c + 1) * 32);
   }
-  if (SAVE) st_global_cs(gmask, mw[0], mw[1], mw[2], mw[3]);
 }
 
 // SAVE: training forward -- every A-operand block (PE, h_0..h_7, feature, PE(dir), view hidden) is also written to the
@@ -254,7 +249,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
   for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(P + w_off(L_ALPHA) + i);
   for (int i = tid; i < 384; i += kThreads) s_wrgb[i] = __ldg(P + w_off(L_RGB) + i);
   cluster_sync_all();                      // barrier inits visible cluster-wide before any remote arrive / multicast commit
-  if (warp == 2) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
+  if (warp == 1) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -327,9 +322,9 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
+  } else if (warp >= 2) {
     // ===== PE + epilogue warps =====
-    const int tile = (warp - 4) >> 2, q = warp & 3;
+    const int tile = (warp - 2) >> 2, q = warp & 3;
     const int row = q * 32 + lane;
     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tile * 256u;
     uint8_t* sAct = smem + kOffA + tile * 65536;
@@ -349,7 +344,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       // training forward: this row's slice of the tile's arena blocks / bit-mask records (tc_arena.cuh)
       uint8_t* tile_base = SAVE ? act_arena + (size_t)((st * 2 + rank) * 2 + tile) * arena::act_tile_bytes() : nullptr;
       uint8_t* grow0 = SAVE ? tile_base + arena::cm_row_offset(row) : nullptr;
-      uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 32 : nullptr;
+      uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 4 : nullptr;
       auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
       auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
       float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
@@ -386,7 +381,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
   }
   tc_fence_before();
   cluster_sync_all();
-  if (warp == 2) tmem_dealloc2(tmem, 512);
+  if (warp == 1) tmem_dealloc2(tmem, 512);
 }
 
 }  // namespace v2

@@ -29,7 +29,7 @@ constexpr int kRowsPerCta = 256, kRowsPerPair = 512;
 constexpr int kStageImage = 32768;
 constexpr int kHalfBytes = 16384;
 constexpr int kRing = 6;        // weight stages in flight
-constexpr int kThreads = 384;
+constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
 constexpr int kNumSteps = 11;      // V1, F, L7, L6, PE5, L5, L4, L3, L2, L1, P0
 constexpr int kNumStages = 42;
 enum Step { S_V1 = 0, S_F = 1, S_L7 = 2, S_L6 = 3, S_PE5 = 4, S_L5 = 5, S_L4 = 6, S_L3 = 7, S_L2 = 8, S_L1 = 9, S_P0 = 10 };
@@ -208,9 +208,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   const int64_t pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
   // step list of this net: the coarse net only receives d sigma: trunk only, no input gradient
   constexpr int kSteps = FINE ? 11 : 7;
-  constexpr int kFineSteps[11] = {S_V1, S_F, S_L7, S_L6, S_PE5, S_L5, S_L4, S_L3, S_L2, S_L1, S_P0};
-  constexpr int kCoarseSteps[7] = {S_L7, S_L6, S_L5, S_L4, S_L3, S_L2, S_L1};
-  auto step_at = [&](int i) { return FINE ? kFineSteps[i] : kCoarseSteps[i]; };
+  // fine: all 11 steps in order; coarse: L7, L6, L5, L4, L3, L2, L1 (arithmetic, not a table: a local array would live in
+  // local memory, and with all of L1 configured as shared memory every lookup would be an L2 round trip)
+  auto step_at = [&](int i) { return FINE ? i : (i < 2 ? i + 2 : i + 3); };
+  static_assert(S_L7 == 2 && S_L6 == 3 && S_L5 == 5 && S_L1 == 9 && S_P0 == 10, "step numbering");
   constexpr int kInitBlocks = FINE ? 2 : 4;                                   // hv (2 blocks) / h7 (4 blocks)
   constexpr int kInitMask = FINE ? arena::kMaskHV : arena::kMaskH + 7;
 
@@ -223,7 +224,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(a.P + w_off(L_ALPHA) + i);
   for (int i = tid; i < 384; i += kThreads) s_wrgb[i] = __ldg(a.P + w_off(L_RGB) + i);
   cluster_sync_all();
-  if (warp == 2) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
+  if (warp == 1) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -290,9 +291,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         }
     }
     __syncwarp();
-  } else if (warp >= 4) {
+  } else if (warp >= 2) {
     // ===== gradient warps: init step + per-step epilogues =====
-    const int tile = (warp - 4) >> 2, q = warp & 3;
+    const int tile = (warp - 2) >> 2, q = warp & 3;
     const int row = q * 32 + lane;
     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tile * 256u;
     uint8_t* sA = smem + kOffA + tile * 65536;
@@ -311,11 +312,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       const bool valid = g < a.M;
       // this row's slice of the tile's gradient-arena blocks and of its saved ReLU bit masks
       uint8_t* grow0 = a.grad_arena + (size_t)T * arena::grad_tile_bytes() + arena::cm_row_offset(row);
-      const uint8_t* mrow0 = a.act_arena + (size_t)T * arena::act_tile_bytes() + arena::act_mask_offset() + row * 32;
+      const uint8_t* mrow0 = a.act_arena + (size_t)T * arena::act_tile_bytes() + arena::act_mask_offset() + row * 4;
       auto load_mask = [&](int layer, uint32_t (&mw)[8]) {
-        const uint4* mp = reinterpret_cast<const uint4*>(mrow0 + layer * arena::kMaskLayerBytes);
-        const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
-        mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+        const uint8_t* mp = mrow0 + layer * arena::kMaskLayerBytes;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mw[w] = __ldg(reinterpret_cast<const uint32_t*>(mp + w * arena::kMaskWordStride));
       };
       const float4 dr = valid ? __ldg(a.d_raw + g) : make_float4(0.f, 0.f, 0.f, 0.f);
       float p[3] = {0.f, 0.f, 0.f}, vd[3];
@@ -413,7 +414,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   }
   tc_fence_before();
   cluster_sync_all();
-  if (warp == 2) tmem_dealloc2(tmem, 512);
+  if (warp == 1) tmem_dealloc2(tmem, 512);
 }
 
 }  // namespace bw

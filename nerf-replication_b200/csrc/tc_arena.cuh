@@ -28,12 +28,14 @@ constexpr int kActFeat = 33;     // feature_linear output (linear), 4 blocks
 constexpr int kActPEDir = 37;    // PE(dir): 27 values, column 63 = 1.0
 constexpr int kActHV = 38;       // views hidden (post-ReLU), 2 blocks
 constexpr int kActBlocks = 40;
-// ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][row 0..127][8 x uint32]
-//      word w of a row covers columns [32 w, 32 w + 32): bit i = column 32 w + 2 i, bit 16 + i = column 32 w + 2 i + 1
+// ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][word 0..7][row 0..127] uint32 (a warp's
+//      word store / load covers 128 contiguous bytes); word w of a row covers columns [32 w, 32 w + 32):
+//      bit i = column 32 w + 2 i, bit 16 + i = column 32 w + 2 i + 1
 constexpr int kMaskH = 0;        // h_l > 0, l = 0..7
 constexpr int kMaskHV = 8;       // views hidden > 0 (words 0..3)
 constexpr int kMaskLayers = 9;
-constexpr int kMaskLayerBytes = 128 * 32;
+constexpr int kMaskWordStride = 128 * 4;       // bytes between consecutive words of one row
+constexpr int kMaskLayerBytes = 8 * kMaskWordStride;
 // ---- gradient arena (written by the dgrad chain) : block slots per tile
 constexpr int kGradZ = 0;        // dZ_l (grad wrt pre-activation of trunk layer l), l = 0..7 : slots 4 l + b
 constexpr int kGradFeat = 32;    // grad wrt feature_linear output, 4 blocks
