@@ -79,6 +79,9 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   if (h->wpack) cudaFree(h->wpack);
   if (h->wpack_bwd) cudaFree(h->wpack_bwd);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->side_fork) cudaEventDestroy(h->side_fork);
+  if (h->side_join) cudaEventDestroy(h->side_join);
   for (int i = 0; i < 2; ++i) {
     if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
     if (h->hev[i]) cudaEventDestroy(h->hev[i]);

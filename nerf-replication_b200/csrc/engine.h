@@ -28,6 +28,8 @@ struct NerfEngine {
                 uint64_t call_id = 0; int64_t n = -1; const float *jitter = nullptr, *u = nullptr; } taps;
 
   // host-path resources (nerf_render_rays_host)
+  cudaStream_t side = nullptr;              // forked work that overlaps a persistent kernel (wgrad heads)
+  cudaEvent_t side_fork = nullptr, side_join = nullptr;
   cudaStream_t hs[2] = {nullptr, nullptr};
   cudaEvent_t hev[2] = {nullptr, nullptr};
   void* pinned[2] = {nullptr, nullptr};

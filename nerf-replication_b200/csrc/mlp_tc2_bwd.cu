@@ -462,7 +462,8 @@ constexpr int kPiece = 8192;
 constexpr int kStageBytes = 5 * kPiece;   // A' 2 pieces | B' main 2 pieces | B' extra 1 piece
 constexpr int kStages = 4;
 constexpr uint32_t kOffStage = 0, kOffXpose = kStages * kStageBytes;          // 163840
-constexpr uint32_t kOffBar = kOffXpose + kFlushWarps * 32 * 33 * 4;           // 197632
+constexpr uint32_t kOffOnes = kOffXpose + kFlushWarps * 32 * 33 * 4;          // 197632: constant B' extra piece, column 63 = 1
+constexpr uint32_t kOffBar = kOffOnes + kPiece;                               // 205824
 constexpr uint32_t kSmemBytes = kOffBar + 128;
 constexpr int kNumJobsFine = 10, kNumJobsCoarse = 8;
 
@@ -507,6 +508,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     mbar_init(&sb.acc_done, 1); mbar_init(&sb.tmem_free, 2 * kFlushWarps);
     fence_barrier_init();
   }
+  // jobs whose layer has no PE input columns still need the bias gradient: their B' extra operand is this constant
+  // piece (64 rows x 64 columns, all zero except column 63 = 1.0) instead of a PE block fetched from the arena
+  for (int i = tid; i < kPiece / 16; i += kThreads) {
+    const bool ones = i >= 7 * 64;                                    // 16-byte chunk i = (column group i / 64, row i % 64)
+    reinterpret_cast<uint4*>(smem + kOffOnes)[i] = make_uint4(0u, 0u, 0u, ones ? 0x3F800000u : 0u);   // bf16 1.0 in column 8*7+7
+  }
+  fence_proxy_async_smem();
   cluster_sync_all();
   if (warp == 1) { tmem_alloc2(&sb.tmem_slot, 512); tmem_relinquish2(); }
   tc_fence_before();
@@ -515,7 +523,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   const uint32_t tmem = sb.tmem_slot;
 
   if (warp == 0) {
-    // ===== producer: per half tile, my halves of dZ^T (A') and X^T (B' main) + the full extra block =====
+    // ===== producer: per half tile, my halves of dZ^T (A') and X^T (B' main) + the extra (PE) piece where the job has one =====
     if (lane == 0) {
       uint32_t it = 0;
       for (int u = pair0; u < a.n_units; u += pair_stride) {
@@ -532,14 +540,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             mbar_wait(&sb.empty[slot], par ^ 1u, 0x810 + slot);
             uint8_t* dst = smem + kOffStage + slot * kStageBytes;
             const uint32_t o = hf * kPiece;
-            mbar_arrive_expect_tx(&sb.full[slot], (jb.main_slot >= 0 ? 5u : 3u) * kPiece);
+            mbar_arrive_expect_tx(&sb.full[slot], (2u + (jb.main_slot >= 0 ? 2u : 0u) + (jb.extra_ncols > 0 ? 1u : 0u)) * kPiece);
             bulk_g2s(dst, gt + o, kPiece, &sb.full[slot]);
             bulk_g2s(dst + kPiece, gt + 16384 + o, kPiece, &sb.full[slot]);
             if (jb.main_slot >= 0) {
               bulk_g2s(dst + 2 * kPiece, mt + o, kPiece, &sb.full[slot]);
               bulk_g2s(dst + 3 * kPiece, mt + 16384 + o, kPiece, &sb.full[slot]);
             }
-            bulk_g2s(dst + 4 * kPiece, xt + o, kPiece, &sb.full[slot]);
+            if (jb.extra_ncols > 0) bulk_g2s(dst + 4 * kPiece, xt + o, kPiece, &sb.full[slot]);
           }
         }
       }
@@ -573,6 +581,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           mbar_wait(&sb.full[slot], par, 0x820 + slot);
           tc_fence_after();
           const uint32_t base = smem_u32(smem + kOffStage + slot * kStageBytes);
+          const uint32_t xbase = jb.extra_ncols > 0 ? base + 4 * kPiece : smem_u32(smem + kOffOnes);
 #pragma unroll
           // core-matrix pieces (tc_arena.cuh) as MN-major operands: LBO = 128 (next 8 rows), SBO = 1024 (next 8 columns;
           // consecutive pieces continue the column index: 8 KB = 8 x SBO), one K = 16 step = 256 bytes
@@ -581,7 +590,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             const uint64_t ad = make_smem_desc(base + ks * 256, 128, 1024, kLayoutNone);
             if (jb.main_slot >= 0)
               umma_ss2(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_main, acc);
-            umma_ss2(tmem + 256, ad, make_smem_desc(base + 4 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_extra, acc);
+            umma_ss2(tmem + 256, ad, make_smem_desc(xbase + ks * 256, 128, 1024, kLayoutNone), idesc_extra, acc);
           }
           umma_commit2(&sb.empty[slot], 0x3);
         }
@@ -637,44 +646,51 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 }
 
 // Heads on CUDA cores: alpha_linear (d sigma^T h7) and rgb_linear (d rgb^T hv) + their biases, straight from the
-// saved arena blocks.  Warp w streams head block w of every tile of its CTA (0..3: h7, 4..5: hv); a lane owns one
-// 16-byte chunk (8 columns) of every fourth row, so a warp instruction reads 8 runs of 64 contiguous bytes.
-__global__ void __launch_bounds__(192) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
-                                                          int64_t M, int n_tiles, int fine, float* __restrict__ G) {
+// saved arena blocks.  One CTA per SM, 12 warps: warp w streams head block w % 6 (0..3: h7, 4..5: hv) of every second
+// tile of its CTA; a lane owns one 16-byte chunk (8 columns) of every fourth row, so a warp instruction reads 8 runs
+// of 64 contiguous bytes.  Partial sums are folded inside the CTA first: the 644 outputs are shared by every CTA, and
+// contended red.global.add is what this kernel would otherwise spend its time on.
+constexpr int kHeadThreads = 384;
+__global__ void __launch_bounds__(kHeadThreads) wgrad_heads_kernel(const uint8_t* __restrict__ act_arena, const float4* __restrict__ d_raw,
+                                                                   int64_t M, int n_tiles, int fine, float* __restrict__ G) {
+  __shared__ float s_red[6][8][28];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hb = warp % 6, tp = warp / 6;
   const int j = lane & 7, rs = lane >> 3;
-  const bool is_rgb = warp >= 4;
-  if (is_rgb && !fine) return;
-  const int slot = is_rgb ? arena::kActHV + (warp - 4) : arena::kActH + 28 + warp;
+  const bool is_rgb = hb >= 4;
+  const bool active = !(is_rgb && !fine);
+  const int slot = is_rgb ? arena::kActHV + (hb - 4) : arena::kActH + 28 + hb;
   float acc[3][8], bs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int k = 0; k < 3; ++k)
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
-  for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-    const uint8_t* blk = act_arena + (size_t)t * arena::act_tile_bytes() + (size_t)slot * 16384;
-    const int64_t g0 = (int64_t)t * 128;
+  if (active) {
+    for (int t = blockIdx.x + gridDim.x * tp; t < n_tiles; t += 2 * gridDim.x) {
+      const uint8_t* blk = act_arena + (size_t)t * arena::act_tile_bytes() + (size_t)slot * 16384;
+      const int64_t g0 = (int64_t)t * 128;
 #pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      const int r = 4 * i + rs;
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(blk + arena::cm_row_offset(r) + j * 1024));
-      const float4 dr = g0 + r < M ? __ldg(d_raw + g0 + r) : make_float4(0.f, 0.f, 0.f, 0.f);
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      for (int i = 0; i < 32; ++i) {
+        const int r = 4 * i + rs;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(blk + arena::cm_row_offset(r) + j * 1024));
+        const float4 dr = g0 + r < M ? __ldg(d_raw + g0 + r) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float x0 = __uint_as_float(w[e] << 16), x1 = __uint_as_float(w[e] & 0xFFFF0000u);
-        if (is_rgb) {
-          acc[0][2 * e] = fmaf(dr.x, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.x, x1, acc[0][2 * e + 1]);
-          acc[1][2 * e] = fmaf(dr.y, x0, acc[1][2 * e]); acc[1][2 * e + 1] = fmaf(dr.y, x1, acc[1][2 * e + 1]);
-          acc[2][2 * e] = fmaf(dr.z, x0, acc[2][2 * e]); acc[2][2 * e + 1] = fmaf(dr.z, x1, acc[2][2 * e + 1]);
-        } else {
-          acc[0][2 * e] = fmaf(dr.w, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.w, x1, acc[0][2 * e + 1]);
+        for (int e = 0; e < 4; ++e) {
+          const float x0 = __uint_as_float(w[e] << 16), x1 = __uint_as_float(w[e] & 0xFFFF0000u);
+          if (is_rgb) {
+            acc[0][2 * e] = fmaf(dr.x, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.x, x1, acc[0][2 * e + 1]);
+            acc[1][2 * e] = fmaf(dr.y, x0, acc[1][2 * e]); acc[1][2 * e + 1] = fmaf(dr.y, x1, acc[1][2 * e + 1]);
+            acc[2][2 * e] = fmaf(dr.z, x0, acc[2][2 * e]); acc[2][2 * e + 1] = fmaf(dr.z, x1, acc[2][2 * e + 1]);
+          } else {
+            acc[0][2 * e] = fmaf(dr.w, x0, acc[0][2 * e]); acc[0][2 * e + 1] = fmaf(dr.w, x1, acc[0][2 * e + 1]);
+          }
         }
+        if (j == 0) { bs[0] += dr.x; bs[1] += dr.y; bs[2] += dr.z; bs[3] += dr.w; }
       }
-      if (j == 0) { bs[0] += dr.x; bs[1] += dr.y; bs[2] += dr.z; bs[3] += dr.w; }
     }
   }
-  // fold the four row groups (lanes l, l^8, l^16, l^24)
+  // fold the four row groups (lanes l, l^8, l^16, l^24), then the two warps of a head block
 #pragma unroll
   for (int k = 0; k < 3; ++k)
 #pragma unroll
@@ -687,19 +703,34 @@ __global__ void __launch_bounds__(192) wgrad_heads_kernel(const uint8_t* __restr
     bs[k] += __shfl_xor_sync(0xffffffffu, bs[k], 8);
     bs[k] += __shfl_xor_sync(0xffffffffu, bs[k], 16);
   }
-  if (rs == 0) {
+  if (tp == 1 && rs == 0) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s_red[hb][j][k * 8 + e] = acc[k][e];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_red[hb][j][24 + k] = bs[k];
+  }
+  __syncthreads();
+  if (tp == 0 && rs == 0 && active) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[k][e] += s_red[hb][j][k * 8 + e];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) bs[k] += s_red[hb][j][24 + k];
     if (is_rgb) {
-      const int c0 = (warp - 4) * 64 + 8 * j;
+      const int c0 = (hb - 4) * 64 + 8 * j;
 #pragma unroll
       for (int k = 0; k < 3; ++k)
 #pragma unroll
         for (int e = 0; e < 8; ++e) atomicAdd(G + w_off(L_RGB) + k * 128 + c0 + e, acc[k][e]);
-      if (warp == 4 && j == 0) for (int k = 0; k < 3; ++k) atomicAdd(G + b_off(L_RGB) + k, bs[k]);
+      if (hb == 4 && j == 0) for (int k = 0; k < 3; ++k) atomicAdd(G + b_off(L_RGB) + k, bs[k]);
     } else {
-      const int c0 = warp * 64 + 8 * j;
+      const int c0 = hb * 64 + 8 * j;
 #pragma unroll
       for (int e = 0; e < 8; ++e) atomicAdd(G + w_off(L_ALPHA) + c0 + e, acc[0][e]);
-      if (warp == 0 && j == 0) atomicAdd(G + b_off(L_ALPHA), bs[3]);
+      if (hb == 0 && j == 0) atomicAdd(G + b_off(L_ALPHA), bs[3]);
     }
   }
 }
@@ -746,9 +777,21 @@ int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const
   a.chunk = memo_chunk[full];
   a.n_units = a.n_jobs * ((a.n_tiles + a.chunk - 1) / a.chunk);
   const int grid = 2 * std::min(a.n_units, pairs);
+  // The heads kernel is independent of the main kernel (disjoint outputs) and small: it runs on a forked stream next
+  // to the persistent main kernel (5 KB of shared memory and 384 threads fit beside it on every SM).
+  if (!h->side) {
+    if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->side_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->side_join, cudaEventDisableTiming) != cudaSuccess)
+      return h->fail(NERF_E_CUDA, "mlp_tc2_wgrad: side stream");
+  }
+  cudaEventRecord(h->side_fork, st);
+  cudaStreamWaitEvent(h->side, h->side_fork, 0);
+  wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms), kHeadThreads, 0, h->side>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M,
+                                                                                    a.n_tiles, full ? 1 : 0, flat_grad_net);
+  cudaEventRecord(h->side_join, h->side);
   mlp_tc2_wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(a);
-  wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms * 4), 192, 0, st>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M,
-                                                                         a.n_tiles, full ? 1 : 0, flat_grad_net);
+  cudaStreamWaitEvent(st, h->side_join, 0);
   h->launches += 2;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_wgrad launch: ") + cudaGetErrorString(e));
