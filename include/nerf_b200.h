@@ -58,6 +58,8 @@ typedef struct NerfConfig {
   int32_t precision;     /* NERF_PRECISION_*                                          */
   float t_near, t_far;   /* 2.0, 6.0                                                  */
   uint64_t seed;         /* Philox seed for in-kernel jitter/u when no arrays given   */
+  int32_t fast_sampling; /* cfg.fast_sampling  (0): ESS/ERT pruning mask on the fine pass (:116-244, :359-374) */
+  float weights_threshold; /* cfg.weights_threshold (0.25): ESS "empty bin" weight threshold (:132-133)        */
 } NerfConfig;
 
 /* Optional outputs / taps of a render call; any pointer may be NULL. */
@@ -117,6 +119,12 @@ int nerf_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, i
 int nerf_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                     const float* u, const float* cdf_in, float* t_fine, int64_t* inds, int64_t* below,
                     int64_t* above, float* cdf_out, float* t_sorted, int32_t* sort_idx, void* stream);
+/* a-M the same with the reference's fast_sampling=True mask (volume_renderer.py:116-133,158-192,359-370):
+ * valid_fine [n,Nf] uint8 = fine_sample_points' valid_mask; mask_sorted [n,Nc+Nf] uint8 = that mask merged with
+ * the all-valid coarse samples and permuted like t_sorted (what Network.forward receives).  Either may be NULL. */
+int nerf_sample_pdf_prune(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf, const float* u,
+                          const float* cdf_in, float weights_threshold, float* t_fine, uint8_t* valid_fine,
+                          uint8_t* mask_sorted, float* t_sorted, int32_t* sort_idx, void* stream);
 
 /* ---- the hot call: Renderer.render, volume_renderer.py:290-432 ------------------------------------ */
 int nerf_render_rays(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n,

@@ -18,7 +18,8 @@ NET_COARSE, NET_FINE = 0, 1
 class NerfConfig(C.Structure):
     _fields_ = [("n_samples", C.c_int32), ("n_importance", C.c_int32), ("white_bkgd", C.c_int32),
                 ("perturb", C.c_int32), ("train_u", C.c_int32), ("precision", C.c_int32),
-                ("t_near", C.c_float), ("t_far", C.c_float), ("seed", C.c_uint64)]
+                ("t_near", C.c_float), ("t_far", C.c_float), ("seed", C.c_uint64),
+                ("fast_sampling", C.c_int32), ("weights_threshold", C.c_float)]
 
 
 class NerfRenderOut(C.Structure):
@@ -44,6 +45,7 @@ SIGNATURES = {
     "nerf_mlp_forward": (_I, [_P, _I, _P, _P, _P, _L, _I, _P, _P]),
     "nerf_composite": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P]),
     "nerf_sample_pdf": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "nerf_sample_pdf_prune": (_I, [_P, _P, _P, _L, _I, _I, _P, _P, _F, _P, _P, _P, _P, _P, _P]),
     "nerf_render_rays": (_I, [_P, _P, _P, _L, _P, _P, C.POINTER(NerfRenderOut), _P]),
     "nerf_render_camera": (_I, [_P, C.POINTER(_D), _I, _I, _D, _D, _D, _L, _L, C.POINTER(NerfRenderOut), _P]),
     "nerf_render_rays_host": (_I, [_P, _P, _P, _L, _P, _P]),

@@ -249,6 +249,18 @@ extern "C" int nerf_sample_pdf(NerfEngine* h, const float* raw_c, const float* t
   return rc ? rc : post(h, "nerf_sample_pdf");
 }
 
+extern "C" int nerf_sample_pdf_prune(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf, const float* u,
+                                     const float* cdf_in, float weights_threshold, float* t_fine, uint8_t* valid_fine,
+                                     uint8_t* mask_sorted, float* t_sorted, int32_t* sort_idx, void* stream) {
+  if (h && n == 0) return NERF_OK;
+  if (!h || !raw_c || !t_c || n < 0 || (!valid_fine && !mask_sorted))
+    return h ? h->fail(NERF_E_INVALID, "nerf_sample_pdf_prune: bad argument") : NERF_E_INVALID;
+  cudaSetDevice(h->device);
+  int rc = launch_sample_pdf(h, raw_c, t_c, n, Nc, Nf, u, false, 0, cdf_in, t_fine, nullptr, nullptr, nullptr, nullptr, t_sorted,
+                             sort_idx, (cudaStream_t)stream, weights_threshold, valid_fine, mask_sorted);
+  return rc ? rc : post(h, "nerf_sample_pdf_prune");
+}
+
 // ---- Renderer.render ----------------------------------------------------------------------------
 struct RenderTaps {   // device workspace of one chunk; kept for the backward pass
   float *t_c = nullptr, *raw_c = nullptr, *t_s = nullptr, *raw_f = nullptr;
@@ -285,9 +297,15 @@ static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n
       if ((rc = h->buf(nb, (size_t)n * Nt, &tp.sort_idx))) return rc;
     }
     const bool tu = c.train_u != 0;
+    uint8_t* prune_mask = nullptr;       // a-M: fine-pass validity mask (fast_sampling); masked samples get raw = 0
+    if (c.fast_sampling) {
+      if (keep) return h->fail(NERF_E_INVALID, "fast_sampling (ESS/ERT mask) is built for the render path only, not the fused training step");
+      char nb[32]; snprintf(nb, 32, "r%d.prune", slot);
+      if ((rc = h->buf(nb, (size_t)n * Nt, &prune_mask))) return rc;
+    }
     if ((rc = launch_sample_pdf(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? u : nullptr, tu && !u, call_id, nullptr, nullptr, nullptr,
-                                nullptr, nullptr, nullptr, tp.t_s, tp.sort_idx, st))) return rc;
-    src.t = tp.t_s; src.S = Nt;
+                                nullptr, nullptr, nullptr, tp.t_s, tp.sort_idx, st, c.weights_threshold, nullptr, prune_mask))) return rc;
+    src.t = tp.t_s; src.S = Nt; src.mask = prune_mask;
     if ((rc = run_mlp(h, NERF_NET_FINE, src, tp.raw_f, keep, st))) return rc;
     launch_composite(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
     if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)

@@ -88,7 +88,8 @@ void launch_composite(NerfEngine* h, const float* raw, const float* t, int64_t n
 int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                       const float* u, bool philox_u, uint64_t call_id, const float* cdf_in, float* t_fine,
                       int64_t* inds, int64_t* below, int64_t* above, float* cdf_out, float* t_sorted,
-                      int32_t* sort_idx, cudaStream_t st);
+                      int32_t* sort_idx, cudaStream_t st, float prune_w_thr = 0.25f, uint8_t* valid_fine = nullptr,
+                      uint8_t* mask_sorted = nullptr);     // a-M: ESS/ERT mask outputs (either non-NULL turns it on)
 // backward stages
 void launch_mse_grad(NerfEngine* h, const float* rgb, const float* gt, int64_t n, float scale,
                      float* d_rgb, float* loss, cudaStream_t st);

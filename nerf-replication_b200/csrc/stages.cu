@@ -180,24 +180,33 @@ void launch_composite(NerfEngine* h, const float* raw, const float* t, int64_t n
 }
 
 // ------------------------------------------------------------------------------------------------
-// Hierarchical sampling.  Per-warp shared memory: t_c[Nc] | cdf[Nc] | keys[Npad] | kidx[Npad].
+// Hierarchical sampling.  Per-warp shared memory: t_c[Nc] | cdf[Nc] | keys[Npad] | kidx[Npad] | bin flags[Nc] | fine valid[Nf]
+// (the last two only serve the ESS/ERT pruning mask of fast_sampling).
 struct PdfSmem {
-  float* tc; float* cdf; float* keys; int* kidx;
+  float* tc; float* cdf; float* keys; int* kidx; int* flags; int* fvalid;
 };
-__device__ __forceinline__ PdfSmem pdf_smem(float* base, int warp, int Nc, int Npad) {
-  float* p = base + (size_t)warp * (2 * Nc + 2 * Npad);
+__host__ __device__ __forceinline__ size_t pdf_smem_words(int Nc, int Nf, int Npad) { return (size_t)3 * Nc + 2 * Npad + Nf; }
+__device__ __forceinline__ PdfSmem pdf_smem(float* base, int warp, int Nc, int Nf, int Npad) {
+  float* p = base + (size_t)warp * pdf_smem_words(Nc, Nf, Npad);
   PdfSmem s; s.tc = p; s.cdf = p + Nc; s.keys = p + 2 * Nc; s.kidx = reinterpret_cast<int*>(p + 2 * Nc + Npad);
+  s.flags = s.kidx + Npad; s.fvalid = s.flags + Nc;
   return s;
 }
 static inline int next_pow2(int v) { int p = 32; while (p < v) p <<= 1; return p; }
 
 // Builds t_c and cdf[0..Nc-2] in shared memory (volume_renderer.py:127-140); returns sum of (w+eps).
 // `wtmp` (>= Nc floats, may alias keys) receives w'_j = w_{j+1}+eps for j in [0,Nc-2).
+// prune != nullptr (a-M, volume_renderer.py:116-133,158-165): flags[k] bit 0 = coarse bin k is "empty" (w < w_thr),
+// bit 1 = the transmittance fell below ert_thr at or before bin k (prefix OR = the reference's cummax); ray_stats
+// receives (sum sigma, max sigma).
+struct PruneArgs { int on; float w_thr, ert_thr; uint8_t* valid_fine; uint8_t* mask_sorted; };
 __device__ __forceinline__ float build_cdf(const float4* __restrict__ raw_c, const float* __restrict__ t_c,
                                            const float* __restrict__ cdf_in, int Nc, int lane,
-                                           float* tc, float* cdf, float* wtmp) {
+                                           float* tc, float* cdf, float* wtmp, const PruneArgs* prune = nullptr,
+                                           int* flags = nullptr, float* ray_stats = nullptr) {
   const int nblk = (Nc + 31) / 32;
-  float carry = 1.0f, ssum = 0.f;
+  float carry = 1.0f, ssum = 0.f, sig_sum = 0.f, sig_max = 0.f;
+  bool ert_seen = false;
   for (int j = 0; j < nblk; ++j) {
     const int i = j * 32 + lane;
     const bool valid = i < Nc;
@@ -212,13 +221,28 @@ __device__ __forceinline__ float build_cdf(const float4* __restrict__ raw_c, con
     const float T = carry * excl;
     carry *= __shfl_sync(0xffffffffu, incl, 31);
     if (valid) tc[i] = ti;
-    if (i >= 1 && i <= Nc - 2) {             // weights[..., 1:-1] + eps
-      const float wp = __fadd_rn(T * a.alpha, kEps);
+    const bool interior = i >= 1 && i <= Nc - 2;
+    const float w = __fmul_rn(T, a.alpha);
+    if (interior) {                          // weights[..., 1:-1] + eps
+      const float wp = __fadd_rn(w, kEps);
       wtmp[i - 1] = wp;
       ssum += wp;
     }
+    if (prune) {
+      sig_sum += sigma; sig_max = fmaxf(sig_max, sigma);
+      const unsigned below_thr = __ballot_sync(0xffffffffu, interior && T < prune->ert_thr);
+      const bool ert = ert_seen || (below_thr & (0xffffffffu >> (31 - lane))) != 0u;
+      ert_seen = ert_seen || below_thr != 0u;
+      if (interior) flags[i - 1] = (w < prune->w_thr ? 1 : 0) | (ert ? 2 : 0);
+    }
   }
   ssum = warp_sum(ssum);
+  if (prune) {
+    sig_sum = warp_sum(sig_sum);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sig_max = fmaxf(sig_max, __shfl_xor_sync(0xffffffffu, sig_max, o));
+    ray_stats[0] = sig_sum; ray_stats[1] = sig_max;
+  }
   __syncwarp();
   const int L = Nc - 1;                       // cdf length
   if (cdf_in) {
@@ -291,13 +315,16 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
                                   uint64_t call_id, const float* __restrict__ cdf_in, float* __restrict__ t_fine,
                                   int64_t* __restrict__ inds, int64_t* __restrict__ below,
                                   int64_t* __restrict__ above, float* __restrict__ cdf_out,
-                                  float* __restrict__ t_sorted, int32_t* __restrict__ sort_idx) {
+                                  float* __restrict__ t_sorted, int32_t* __restrict__ sort_idx, PruneArgs prune) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  PdfSmem s = pdf_smem(smem, warp, Nc, Npad);
+  PdfSmem s = pdf_smem(smem, warp, Nc, Nf, Npad);
   const int Nt = Nc + Nf;
   for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerBlock + warp; ray < n; ray += (int64_t)gridDim.x * kWarpsPerBlock) {
-    build_cdf(raw_c + ray * Nc, t_c + ray * Nc, cdf_in ? cdf_in + ray * (Nc - 1) : nullptr, Nc, lane, s.tc, s.cdf, s.keys);
+    float stats[2] = {0.f, 0.f};
+    build_cdf(raw_c + ray * Nc, t_c + ray * Nc, cdf_in ? cdf_in + ray * (Nc - 1) : nullptr, Nc, lane, s.tc, s.cdf, s.keys,
+              prune.on ? &prune : nullptr, s.flags, stats);
+    const bool empty_ray = stats[0] < 1e-3f, object_ray = stats[1] > 0.5f;      // volume_renderer.py:116-122
     if (cdf_out) for (int k = lane; k < Nc - 1; k += 32) cdf_out[ray * (Nc - 1) + k] = s.cdf[k];
     __syncwarp();
     for (int k = lane; k < Nc; k += 32) { s.keys[k] = s.tc[k]; s.kidx[k] = k; }
@@ -309,14 +336,23 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
       if (inds) inds[o] = f.inds;
       if (below) below[o] = f.below;
       if (above) above[o] = f.above;
+      if (prune.on) {      // ESS (:170-186): object rays need both neighbour bins empty, background rays either; ERT (:158-168)
+        const int fb = s.flags[f.below], fa = s.flags[f.above];
+        const bool ess = object_ray ? ((fb & fa) & 1) != 0 : ((fb | fa) & 1) != 0;
+        const bool valid = !(ess || (fb & 2) != 0) && !empty_ray;
+        s.fvalid[k] = valid ? 1 : 0;
+        if (prune.valid_fine) prune.valid_fine[o] = valid ? 1 : 0;
+      }
     }
     for (int k = Nt + lane; k < Npad; k += 32) { s.keys[k] = __int_as_float(0x7f800000); s.kidx[k] = 0x7fffffff; }
     __syncwarp();
-    if (t_sorted || sort_idx) {
+    if (t_sorted || sort_idx || (prune.on && prune.mask_sorted)) {
       warp_bitonic_sort(s.keys, s.kidx, Npad, lane);
       for (int k = lane; k < Nt; k += 32) {
         if (t_sorted) t_sorted[ray * Nt + k] = s.keys[k];
         if (sort_idx) sort_idx[ray * Nt + k] = s.kidx[k];
+        // coarse samples stay valid; fine samples carry their flag through the same permutation (:359-370)
+        if (prune.on && prune.mask_sorted) prune.mask_sorted[ray * Nt + k] = s.kidx[k] < Nc ? 1 : (uint8_t)s.fvalid[s.kidx[k] - Nc];
       }
     }
     __syncwarp();
@@ -326,15 +362,18 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
 int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                       const float* u, bool philox_u, uint64_t call_id, const float* cdf_in, float* t_fine,
                       int64_t* inds, int64_t* below, int64_t* above, float* cdf_out, float* t_sorted,
-                      int32_t* sort_idx, cudaStream_t st) {
+                      int32_t* sort_idx, cudaStream_t st, float prune_w_thr, uint8_t* valid_fine, uint8_t* mask_sorted) {
   if (Nc < 4 || Nf < 1 || Nc + Nf > 4096) return h->fail(NERF_E_INVALID, "sample_pdf: need Nc>=4, Nf>=1, Nc+Nf<=4096");
   if (n <= 0) return NERF_OK;
   const int Npad = next_pow2(Nc + Nf);
-  const size_t smem = (size_t)kWarpsPerBlock * (2 * Nc + 2 * Npad) * sizeof(float);
+  PruneArgs prune;
+  prune.on = (valid_fine || mask_sorted) ? 1 : 0; prune.w_thr = prune_w_thr; prune.ert_thr = 0.45f;   // ert_threshold default (:98)
+  prune.valid_fine = valid_fine; prune.mask_sorted = mask_sorted;
+  const size_t smem = (size_t)kWarpsPerBlock * pdf_smem_words(Nc, Nf, Npad) * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(sample_pdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   sample_pdf_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw_c), t_c, n, Nc, Nf, Npad, u, philox_u ? 1 : 0, h->cfg.seed, call_id, cdf_in,
-      t_fine, inds, below, above, cdf_out, t_sorted, sort_idx);
+      t_fine, inds, below, above, cdf_out, t_sorted, sort_idx, prune);
   h->launches++;
   return NERF_OK;
 }

@@ -33,13 +33,14 @@ class Engine:
     """Owns a NerfEngine handle.  cfg keys mirror Renderer.__init__ (volume_renderer.py:9-24)."""
 
     def __init__(self, n_samples=64, n_importance=128, white_bkgd=True, perturb=False, train_u=False,
-                 precision="bf16", t_near=2.0, t_far=6.0, seed=0, device=None):
+                 precision="bf16", t_near=2.0, t_far=6.0, seed=0, device=None, fast_sampling=False, weights_threshold=0.25):
         if not torch.cuda.is_available():
             raise EngineError("nerf_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         self.lib = L.load()
         self.device = torch.cuda.current_device() if device is None else int(device)
         self.cfg = L.NerfConfig()
-        self._set_cfg_fields(n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed)
+        self._set_cfg_fields(n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed,
+                             fast_sampling, weights_threshold)
         h = C.c_void_p()
         rc = self.lib.nerf_create(C.byref(self.cfg), self.device, C.byref(h))
         if rc != 0:
@@ -48,12 +49,14 @@ class Engine:
         self._flat = None
 
     # -- plumbing -------------------------------------------------------------------------------
-    def _set_cfg_fields(self, n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed):
+    def _set_cfg_fields(self, n_samples, n_importance, white_bkgd, perturb, train_u, precision, t_near, t_far, seed,
+                        fast_sampling=False, weights_threshold=0.25):
         c = self.cfg
         c.n_samples, c.n_importance = int(n_samples), int(n_importance)
         c.white_bkgd, c.perturb, c.train_u = int(bool(white_bkgd)), int(bool(perturb)), int(bool(train_u))
         c.precision = {"bf16": L.PRECISION_BF16, "fp32": L.PRECISION_FP32}[precision]
         c.t_near, c.t_far, c.seed = float(t_near), float(t_far), int(seed)
+        c.fast_sampling, c.weights_threshold = int(bool(fast_sampling)), float(weights_threshold)
 
     @property
     def precision(self):
@@ -62,7 +65,8 @@ class Engine:
     def configure(self, **kw):
         c = self.cfg
         cur = dict(n_samples=c.n_samples, n_importance=c.n_importance, white_bkgd=c.white_bkgd, perturb=c.perturb,
-                   train_u=c.train_u, precision=self.precision, t_near=c.t_near, t_far=c.t_far, seed=c.seed)
+                   train_u=c.train_u, precision=self.precision, t_near=c.t_near, t_far=c.t_far, seed=c.seed,
+                   fast_sampling=c.fast_sampling, weights_threshold=c.weights_threshold)
         cur.update(kw)
         self._set_cfg_fields(**cur)
         self._check(self.lib.nerf_set_config(self.h, C.byref(self.cfg)))
@@ -175,6 +179,21 @@ class Engine:
                                              out["t_fine"].data_ptr(), out["inds"].data_ptr(), out["below"].data_ptr(),
                                              out["above"].data_ptr(), out["cdf"].data_ptr(), out["t_sorted"].data_ptr(),
                                              out["sort_idx"].data_ptr(), self._stream()))
+        return out
+
+    def sample_pdf_prune(self, raw_c, t_c, n_importance, weights_threshold=0.25, u=None, cdf_in=None):
+        """a-M: sample_pdf with the reference's fast_sampling mask -> t_fine, valid (bool [n,Nf]), mask_sorted (bool [n,Nc+Nf]),
+        t_sorted, sort_idx."""
+        n, Nc = t_c.shape
+        Nf, dev = n_importance, t_c.device
+        out = dict(t_fine=torch.empty(n, Nf, device=dev), valid=torch.empty(n, Nf, dtype=torch.uint8, device=dev),
+                   mask_sorted=torch.empty(n, Nc + Nf, dtype=torch.uint8, device=dev),
+                   t_sorted=torch.empty(n, Nc + Nf, device=dev), sort_idx=torch.empty(n, Nc + Nf, dtype=torch.int32, device=dev))
+        self._check(self.lib.nerf_sample_pdf_prune(self.h, self._p(raw_c, name="raw_c"), self._p(t_c, name="t_c"), n, Nc, Nf,
+                                                   self._p(u, name="u"), self._p(cdf_in, name="cdf_in"), float(weights_threshold),
+                                                   out["t_fine"].data_ptr(), out["valid"].data_ptr(), out["mask_sorted"].data_ptr(),
+                                                   out["t_sorted"].data_ptr(), out["sort_idx"].data_ptr(), self._stream()))
+        out["valid"], out["mask_sorted"] = out["valid"].bool(), out["mask_sorted"].bool()
         return out
 
     # -- render ---------------------------------------------------------------------------------

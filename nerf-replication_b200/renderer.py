@@ -53,13 +53,13 @@ class Renderer:
         self.fast_sampling = bool(knob(cfg, "fast_sampling", False))
         self.weights_threshold = knob(cfg, "weights_threshold", 0.25)
         self.return_dict = bool(getattr(cfg, "return_dict", False))
-        if self.fast_sampling:
-            raise NotImplementedError("fast_sampling (ESS/ERT pruning, volume_renderer.py:116-244) is not built yet; "
-                                      "there is no fallback")
+        # fast_sampling (ESS/ERT, volume_renderer.py:116-244,359-374): the engine builds the reference's validity mask in the
+        # sample_pdf kernel and zeroes the masked fine samples' raw output (render path; the fused training step refuses it)
 
     def _engine(self):
         return self.net.engine(n_samples=self.N_samples, n_importance=self.N_importance, white_bkgd=self.white_bkgd,
-                               perturb=self.perturb, train_u=(self.task == "train"))
+                               perturb=self.perturb, train_u=(self.task == "train"), fast_sampling=self.fast_sampling,
+                               weights_threshold=float(self.weights_threshold))
 
     def render(self, batch, return_dict=None, jitter=None, u=None):
         rays_o, rays_d = batch["rays_o"], batch["rays_d"]

@@ -30,11 +30,14 @@ def ref_network(ref, sd):
     return net
 
 
-def run_reference(ref, sd, rays_o, rays_d, n_samples, n_importance, white_bkgd, grad=False):
-    """Unmodified reference render with recording wrappers around its own methods."""
+def run_reference(ref, sd, rays_o, rays_d, n_samples, n_importance, white_bkgd, grad=False, fast=None):
+    """Unmodified reference render with recording wrappers around its own methods.
+    fast = weights_threshold turns on the reference's fast_sampling (ESS/ERT) path."""
     net = ref_network(ref, sd)
     r = ref.Renderer(net)
     r.N_samples, r.N_importance, r.white_bkgd = n_samples, n_importance, white_bkgd
+    if fast is not None:
+        r.fast_sampling, r.weights_threshold = True, fast
     taps = {"net_out": []}
     orig_fwd, orig_fine, orig_strat = net.forward, r.fine_sample_points, r.stratified_sample_points_from_rays
 
@@ -46,6 +49,8 @@ def run_reference(ref, sd, rays_o, rays_d, n_samples, n_importance, white_bkgd, 
     def fine(**kw):
         pts, t_fine, mask = orig_fine(**kw)
         taps["t_fine"] = t_fine
+        if mask is not None:
+            taps["valid_mask"] = mask
         return pts, t_fine, mask
 
     def strat(**kw):
@@ -102,8 +107,42 @@ def render_case(ref, name, sd, rays_o, rays_d, n_samples=64, n_importance=128, w
     print("golden %-28s rays=%d  rgb[0]=%s depth[0]=%.6f" % (name, rays_o.shape[0], rt["rgb_map"][0].tolist(), rt["depth_map"][0]))
 
 
+def fast_case(ref, name, sd, rays_o, rays_d, thr=0.25):
+    """a-M: the reference's fast_sampling=True path (ESS/ERT masks) vs the restatement, bit for bit."""
+    _, rt = run_reference(ref, sd, rays_o, rays_d, 64, 128, True, fast=thr)
+    ot = {}
+    with torch.no_grad():
+        O.render(sd, rays_o, rays_d, 64, 128, True, taps=ot, fast_sampling=True, weights_threshold=thr)
+    keys = ["t_coarse", "raw_coarse", "t_fine", "valid_mask", "raw_fine", "rgb_map", "depth_map"]
+    for k in keys:
+        same(rt[k], ot[k], "%s/%s" % (name, k))
+    out = {k: rt[k].numpy() for k in keys}
+    out.update(rays_o=rays_o.numpy(), rays_d=rays_d.numpy(), weights_threshold=thr)
+    for k in ("cdf", "below", "above", "sort_idx", "valid_sorted", "empty_ray", "object_ray"):
+        out[k] = ot[k].numpy()
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), **out)
+    m = rt["valid_mask"]
+    print("golden %-28s rays=%d  valid fine points %d / %d, empty rays %d, object rays %d" % (
+        name, rays_o.shape[0], int(m.sum()), m.numel(), int(ot["empty_ray"].sum()), int(ot["object_ray"].sum())))
+
+
+def fast_cases(ref):
+    c2w = O.lego_pose(0)
+    pix64 = np.linspace(0, 9999, 64).astype(np.int64)
+    ro, rd = map(torch.from_numpy, O.get_rays_np(c2w, 100, 100, pix64))
+    fast_case(ref, "fast_sharp_64rays", O.init_state_dict(0, sharp=True), ro, rd)
+    fast_case(ref, "fast_sharp_thr05_64rays", O.init_state_dict(0, sharp=True), ro, rd, 0.05)
+    fast_case(ref, "fast_fog_64rays", O.fog_state_dict(0), ro, rd, 0.02)
+    fast_case(ref, "fast_seed0_64rays", O.init_state_dict(0), ro, rd)
+    fast_case(ref, "fast_thin_64rays", O.fog_state_dict(0, bias=-0.015), ro, rd, 2e-4)     # 26 empty rays, background rule
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
+    if "--fast-only" in sys.argv:        # adds the a-M goldens without rewriting the others
+        torch.set_num_threads(1)
+        fast_cases(ref_loader.load_reference())
+        return
     torch.set_num_threads(1)   # bit-stable reductions
     ref = ref_loader.load_reference()
 
@@ -158,6 +197,7 @@ def main():
     render_case(ref, "render_sharp_coarse_only", sd_sharp, ro[:16], rd[:16], 64, 0)
     render_case(ref, "render_sharp_black_bkgd", sd_sharp, ro[:16], rd[:16], 64, 128, False)
     render_case(ref, "render_sharp_128_256", sd_sharp, ro[:8], rd[:8], 128, 256)
+    fast_cases(ref)
 
     # -- training: reference render under autograd + the restated loss/clip/Adam loop, 4 steps
     #    (trainer.py:53 is broken as shipped -- SURVEY fact 9 -- so the loop is the composition the

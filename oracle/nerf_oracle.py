@@ -184,11 +184,15 @@ def weights_computation(sigma, t):
     return T, T * alpha                                                          # :94
 
 
-# a-H  hierarchical sampling (volume_renderer.py:98-272), default fast_sampling=False path
-def sample_pdf(sigma_c, t_c, n_importance, u=None, eps=1e-5, taps=None):
+# a-H  hierarchical sampling (volume_renderer.py:98-272); a-M: the ESS/ERT validity mask of fast_sampling=True
+def sample_pdf(sigma_c, t_c, n_importance, u=None, eps=1e-5, taps=None, fast_sampling=False,
+               weights_threshold=0.25, ert_threshold=0.45):
     n_samples = t_c.shape[-1]
-    _, w = weights_computation(sigma_c, t_c)                    # :127
-    w = w[..., 1:-1] + eps                                      # :128, :137
+    T, w = weights_computation(sigma_c, t_c)                    # :127
+    w = w[..., 1:-1]                                            # :128
+    T = T[..., 1:-1]                                            # :129
+    empty_bins = w < weights_threshold                          # :132-133 (ESS: bins whose coarse weight is small)
+    w = w + eps                                                 # :137
     pdf = w / torch.sum(w, -1, keepdim=True)
     cdf = torch.cumsum(pdf, -1)
     cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)  # [N, Nc-1]
@@ -207,7 +211,24 @@ def sample_pdf(sigma_c, t_c, n_importance, u=None, eps=1e-5, taps=None):
     t_fine = b0 + tt * (b1 - b0)                                # :263-264
     if taps is not None:
         taps.update(cdf=cdf, inds=inds, below=below, above=above, bins=bins)
-    return t_fine
+    if not fast_sampling:
+        return t_fine
+    # ---- a-M  ESS / ERT pruning mask (:116-123, :158-192); the debug prints (:195-244) are not restated
+    empty_ray = sigma_c.sum(dim=-1) < 1e-3                      # :116-117
+    object_ray = sigma_c.max(dim=-1).values > 0.5               # :120-122
+    ert_base = T < ert_threshold                                # :160
+    ert_padded = torch.cat([torch.zeros_like(ert_base[:, :1]), ert_base], dim=1)
+    ert_bins = torch.cummax(ert_padded, dim=1)[0][:, 1:]        # :161-165: once T fell below the threshold, all later bins
+    ert_non_valid = torch.gather(ert_bins, 1, below)            # :167-168
+    below_empty, above_empty = torch.gather(empty_bins, 1, below), torch.gather(empty_bins, 1, above)   # :172-174
+    ess_non_valid = torch.where(object_ray[:, None].expand_as(below_empty),
+                                below_empty & above_empty,      # object rays: both neighbours empty  (:176)
+                                below_empty | above_empty)      # background rays: either             (:178)
+    valid = ~(ess_non_valid | ert_non_valid)                    # :189-190
+    valid[empty_ray] = False                                    # :191
+    if taps is not None:
+        taps.update(valid_mask=valid, empty_ray=empty_ray, object_ray=object_ray)
+    return t_fine, valid
 
 
 # a-J composite (volume_renderer.py:414-430)
@@ -226,7 +247,7 @@ def composite(raw, t, white_bkgd=True):
 # ----------------------------------------------------------------------------------------------
 # Renderer.render (volume_renderer.py:290-432)
 def render(sd, rays_o, rays_d, n_samples=64, n_importance=128, white_bkgd=True,
-           jitter=None, u=None, taps=None, chunk=512):
+           jitter=None, u=None, taps=None, chunk=512, fast_sampling=False, weights_threshold=0.25):
     """rays_o/rays_d [N,3] fp32 -> (rgb [N,3], depth [N]) of the final pass.  ``taps`` (dict)
     receives every intermediate; ``jitter``/``u`` inject the perturb / train-mode random numbers."""
     N = rays_o.shape[0]
@@ -238,12 +259,21 @@ def render(sd, rays_o, rays_d, n_samples=64, n_importance=128, white_bkgd=True,
     tp.update(t_coarse=t_c, raw_coarse=raw_c, viewdirs=viewdirs)
     if n_importance > 0:
         sigma_c = F.relu(raw_c[..., 3])                              # :335-338
-        t_f = sample_pdf(sigma_c, t_c, n_importance, u, taps=tp)
+        valid_sorted = None
+        if fast_sampling:
+            t_f, valid_f = sample_pdf(sigma_c, t_c, n_importance, u, taps=tp, fast_sampling=True,
+                                      weights_threshold=weights_threshold)
+        else:
+            t_f = sample_pdf(sigma_c, t_c, n_importance, u, taps=tp)
         pts_f = points_on_rays(rays_o, rays_d, t_f)
         depth = torch.cat([t_c, t_f], 1)
         depth, idx = torch.sort(depth, dim=-1)                       # :353
         pts = torch.gather(torch.cat([pts_c, pts_f], 1), 1, idx.unsqueeze(-1).expand(-1, -1, 3))
-        raw = torch.cat([network_forward(sd, pts[:, j:j + 64], viewdirs, None, "fine", chunk)
+        if fast_sampling:                                            # :359-370: coarse samples stay valid, same permutation
+            valid_sorted = torch.gather(torch.cat([torch.ones(N, n_samples, dtype=torch.bool), valid_f], 1), 1, idx)
+            tp.update(valid_sorted=valid_sorted)
+        raw = torch.cat([network_forward(sd, pts[:, j:j + 64], viewdirs,
+                                         None if valid_sorted is None else valid_sorted[:, j:j + 64], "fine", chunk)
                          for j in range(0, pts.shape[1], 64)], 1)    # :386-397 (sample blocks of 64)
         tp.update(t_fine=t_f, depth_sorted=depth, sort_idx=idx, raw_fine=raw)
         rgb_c, depth_c, acc_c, _ = composite(raw_c, t_c, white_bkgd)  # extension maps (fact 3)

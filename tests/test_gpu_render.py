@@ -159,3 +159,39 @@ def test_empty_and_chunked_render(oracle):
     assert maxabs(full["rgb"][65536 - 8:], tail["rgb"]) == 0.0
     assert torch.isfinite(full["rgb"]).all() and torch.isfinite(full["depth"]).all()
     eng.close()
+
+
+FAST_CASES = {"fast_sharp_64rays": ("sharp", 0.25), "fast_sharp_thr05_64rays": ("sharp", 0.05), "fast_fog_64rays": ("fog", 0.02),
+              "fast_seed0_64rays": ("seed0", 0.25), "fast_thin_64rays": ("thin", 2e-4)}
+
+
+@pytest.mark.parametrize("case", sorted(FAST_CASES))
+def test_render_fast_sampling_fp32_vs_reference_golden(oracle, case):
+    """a-M end to end: Renderer with cfg.fast_sampling (ESS/ERT mask, masked fine samples -> raw = 0) against the
+    reference run with fast_sampling=True.  A mask bit is a threshold test on a coarse weight / transmittance, so a
+    ray whose value sits within fp32 rounding of the threshold may legitimately flip one sample: at most one ray of
+    the 64 may miss the 1e-5 gate."""
+    from test_oracle import fast_state_dict
+    g = load_golden(case)
+    kind, thr = FAST_CASES[case]
+    eng = make_engine(oracle, fast_state_dict(oracle, kind), "fp32", fast_sampling=True, weights_threshold=thr)
+    out = eng.render_rays(dev(g["rays_o"]), dev(g["rays_d"]))
+    torch.cuda.synchronize()
+    d = (out["rgb"].cpu() - torch.from_numpy(g["rgb_map"])).abs().max(dim=1).values
+    print(case, "rays over 1e-5:", int((d > FP32_RGB_TOL).sum()), "max", float(d.max()))
+    assert int((d > FP32_RGB_TOL).sum()) <= 1
+    # masking must matter in the cases where the mask removes samples: the unmasked render differs
+    if g["valid_mask"].sum() < g["valid_mask"].size and kind != "seed0":
+        eng.configure(fast_sampling=False)
+        plain = eng.render_rays(dev(g["rays_o"]), dev(g["rays_d"]))
+        assert maxabs(plain["rgb"], g["rgb_map"]) > 10 * FP32_RGB_TOL
+    eng.close()
+
+
+def test_fast_sampling_refused_by_fused_training(oracle):
+    eng = make_engine(oracle, oracle.init_state_dict(0), "bf16", fast_sampling=True)
+    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, 8, 100, 100)
+    grad = torch.zeros(eng._keep.numel(), device="cuda")
+    with pytest.raises(Exception, match="render path only"):
+        eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad)
+    eng.close()

@@ -168,3 +168,25 @@ def test_full_size_properties(eng, oracle):
     assert maxabs(rgb_b + (1 - acc)[:, None], rgb_w) <= 1e-6
     assert float(acc.max()) <= 1 + 1e-5 and float(w.min()) >= 0
     assert maxabs(w.sum(-1), acc) <= 1e-5
+
+
+FAST_CASES = {"fast_sharp_64rays": 0.25, "fast_sharp_thr05_64rays": 0.05, "fast_fog_64rays": 0.02, "fast_seed0_64rays": 0.25,
+              "fast_thin_64rays": 2e-4}
+
+
+@pytest.mark.parametrize("case", sorted(FAST_CASES))
+def test_fast_sampling_mask(eng, case):
+    """a-M: ESS/ERT validity mask (volume_renderer.py:116-133,158-192,359-370) vs the reference goldens.  With the
+    oracle's cdf injected the bin indices are bit-exact, so the mask can only differ where a coarse weight /
+    transmittance sits within rounding of its threshold (the warp scan multiplies in a different order)."""
+    g = load_golden(case)
+    out = eng.sample_pdf_prune(dev(g["raw_coarse"]), dev(g["t_coarse"]), 128, FAST_CASES[case], cdf_in=dev(g["cdf"]))
+    assert torch.equal(out["t_fine"].cpu(), torch.from_numpy(g["t_fine"]))
+    valid, ref = out["valid"].cpu(), torch.from_numpy(g["valid_mask"])
+    assert int((valid != ref).sum()) <= 2, "mask differs in %d of %d fine samples" % (int((valid != ref).sum()), ref.numel())
+    # sorted mask: coarse samples valid, fine flags carried by the merge permutation
+    idx = out["sort_idx"].cpu().long()
+    merged = torch.cat([torch.ones(ref.shape[0], 64, dtype=torch.bool), valid], 1)
+    assert torch.equal(out["mask_sorted"].cpu(), torch.gather(merged, 1, idx))
+    if torch.equal(valid, ref):
+        assert torch.equal(out["mask_sorted"].cpu(), torch.from_numpy(g["valid_sorted"]))

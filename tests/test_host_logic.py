@@ -30,9 +30,9 @@ def test_renderer_reads_reference_keys():
     assert r.perturb is False                            # task != "train" forces perturb off (:21-22)
     cfg.task = "train"
     assert Renderer(net=None, cfg=cfg).perturb is True
-    cfg.fast_sampling = True
-    with pytest.raises(NotImplementedError):
-        Renderer(net=None, cfg=cfg)
+    cfg.fast_sampling = True                             # a-M: accepted, same keys / defaults as the reference (:23-24)
+    r = Renderer(net=None, cfg=cfg)
+    assert r.fast_sampling is True and r.weights_threshold == 0.25
 
 
 def test_network_surface_matches_reference(oracle):

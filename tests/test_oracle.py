@@ -67,6 +67,35 @@ def test_render_golden(oracle, case):
         assert g["below"].max() <= int(g["n_samples"]) - 3 and g["above"].max() <= int(g["n_samples"]) - 3
 
 
+FAST_CASES = {"fast_sharp_64rays": ("sharp", 0.25), "fast_sharp_thr05_64rays": ("sharp", 0.05), "fast_fog_64rays": ("fog", 0.02),
+              "fast_seed0_64rays": ("seed0", 0.25), "fast_thin_64rays": ("thin", 2e-4)}
+
+
+def fast_state_dict(oracle, kind):
+    return {"sharp": lambda: oracle.init_state_dict(0, sharp=True), "fog": lambda: oracle.fog_state_dict(0),
+            "seed0": lambda: oracle.init_state_dict(0), "thin": lambda: oracle.fog_state_dict(0, bias=-0.015)}[kind]()
+
+
+@pytest.mark.parametrize("case", sorted(FAST_CASES))
+def test_fast_sampling_golden(oracle, case):
+    """a-M: the ESS/ERT mask restatement against outputs of the reference run with fast_sampling=True
+    (oracle/make_golden.py --fast-only): mask, masked raw and maps bit for bit."""
+    g = load_golden(case)
+    kind, thr = FAST_CASES[case]
+    assert float(g["weights_threshold"]) == pytest.approx(thr)
+    torch.set_num_threads(1)
+    taps = {}
+    with torch.no_grad():
+        oracle.render(fast_state_dict(oracle, kind), torch.from_numpy(g["rays_o"]), torch.from_numpy(g["rays_d"]),
+                      taps=taps, fast_sampling=True, weights_threshold=thr)
+    for k in ("t_fine", "valid_mask", "valid_sorted", "raw_fine", "rgb_map", "depth_map"):
+        np.testing.assert_array_equal(taps[k].numpy(), g[k], err_msg=k)
+    raw = torch.from_numpy(g["raw_fine"])
+    assert (raw[~torch.from_numpy(g["valid_sorted"])] == 0).all()          # masked points -> raw = 0 (network.py:235)
+    empty = torch.from_numpy(g["empty_ray"])
+    assert not torch.from_numpy(g["valid_mask"])[empty].any()              # empty rays keep no fine sample (:191)
+
+
 def test_train_golden(oracle):
     g = load_golden("train_sharp_32rays")
     torch.set_num_threads(1)
