@@ -262,14 +262,15 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li) {
           const uint32_t bytes = (uint32_t)sched_n(li) * 64u;                 // half of the stage: N/2 rows x 128 B
-          for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
-            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-            mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
-            mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
-            bulk_g2s(smem + kOffW + slot * kHalfBytes,
-                     reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes,
-                     bytes, &sb.w_full[slot]);
-          }
+          for (int rep = 0; rep < (SAVE ? 2 : 1); ++rep)                      // training: once per tile (see the issuer)
+            for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
+              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+              mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
+              mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
+              bulk_g2s(smem + kOffW + slot * kHalfBytes,
+                       reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes,
+                       bytes, &sb.w_full[slot]);
+            }
         }
       }
     }
@@ -279,7 +280,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t st = pair0; st < n_pair; st += pair_stride)
-        for (int s = 0; s < kNumStages; ++s, ++it) {
+        for (int s = 0; s < (SAVE ? 2 : 1) * kNumStages; ++s, ++it) {
           const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
           mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
           mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
@@ -295,28 +296,49 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
         for (int li = 0; li < kNumSched; ++li, ++lc) {
           const int nkb = sched_nkb(li);
           const uint32_t idesc = make_idesc_bf16(256, sched_n(li));
-          for (int kb = 0; kb < nkb; ++kb, ++it) {
-            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-            mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
-            tc_fence_after();
-            int ablk;   // A source of this k-block: -1 = PE buffer, else hidden-activation block
-            if (li == 0) ablk = -1;
-            else if (li == 5) ablk = kb - 1;
-            else if (li == 9) ablk = kb < 4 ? kb : -1;
-            else ablk = kb;
+          // A source of k-block kb: -1 = PE buffer, else hidden-activation block
+          auto a_block = [&](int kb) { return li == 0 ? -1 : li == 5 ? kb - 1 : li == 9 ? (kb < 4 ? kb : -1) : kb; };
+          auto issue = [&](int tile, int kb, uint32_t slot) {
+            const int ablk = a_block(kb);
+            const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
+            const uint32_t b_base = sW + slot * kHalfBytes;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
+                       make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+            }
+          };
+          if (SAVE) {
+            // Training forward: one tile's whole layer, then the other's -- the layer's weights are streamed twice (L2
+            // hits) so that tile Y's MMAs run under tile X's long (arena-storing) epilogue.
 #pragma unroll
             for (int tile = 0; tile < 2; ++tile) {
-              if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
-              const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
-              const uint32_t b_base = sW + slot * kHalfBytes;
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk) {
-                umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
-                         make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+              mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
+              tc_fence_after();
+              for (int kb = 0; kb < nkb; ++kb, ++it) {
+                const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+                mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+                tc_fence_after();
+                issue(tile, kb, slot);
+                umma_commit2(&sb.w_empty[slot], 0x3);
               }
-              if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+              umma_commit2(&sb.acc_full[tile], 0x3);
             }
-            umma_commit2(&sb.w_empty[slot], 0x3);
+          } else {
+            // Render: every weight stage feeds both tiles before it is released (half the weight traffic; with the
+            // 3-slot ring the per-tile order above starves the tensor pipe: 1075 vs 1128 TFLOP/s measured).
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+              mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+              tc_fence_after();
+#pragma unroll
+              for (int tile = 0; tile < 2; ++tile) {
+                if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+                issue(tile, kb, slot);
+                if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+              }
+              umma_commit2(&sb.w_empty[slot], 0x3);
+            }
           }
         }
       }

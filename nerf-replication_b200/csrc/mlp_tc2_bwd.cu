@@ -238,6 +238,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         for (int i = 0; i < kSteps; ++i) {
           const int s = step_at(i);
           const uint32_t bytes = (uint32_t)step_n(s) * 64u;
+          for (int rep = 0; rep < 2; ++rep)            // once per tile: see the issuer
           for (int kb = 0; kb < step_nkb(s); ++kb, ++it) {
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
             mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
@@ -255,7 +256,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       uint32_t it = 0;
       for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
         for (int i = 0; i < kSteps; ++i)
-          for (int kb = 0; kb < step_nkb(step_at(i)); ++kb, ++it) {
+          for (int kb = 0; kb < 2 * step_nkb(step_at(i)); ++kb, ++it) {
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
             mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
             mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
@@ -271,22 +272,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         for (int i = 0; i < kSteps; ++i, ++lc) {
           const int s = step_at(i), nkb = step_nkb(s);
           const uint32_t idesc = make_idesc_bf16(256, step_n(s));
-          for (int kb = 0; kb < nkb; ++kb, ++it) {
-            const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-            mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
-            tc_fence_after();
+          // one tile's whole step, then the other's (the step's weights are streamed twice, L2 hits): tile Y's MMAs run
+          // under tile X's epilogue instead of both accumulators finishing -- and being drained -- together
 #pragma unroll
-            for (int tile = 0; tile < 2; ++tile) {
-              if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+          for (int tile = 0; tile < 2; ++tile) {
+            mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
+            tc_fence_after();
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+              mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+              tc_fence_after();
               const uint32_t a_base = sA + tile * 65536u + (uint32_t)kb * 16384u;
               const uint32_t b_base = sW + slot * kHalfBytes;
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
                 umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
                          make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
-              if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+              umma_commit2(&sb.w_empty[slot], 0x3);
             }
-            umma_commit2(&sb.w_empty[slot], 0x3);
+            umma_commit2(&sb.acc_full[tile], 0x3);
           }
         }
     }
