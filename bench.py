@@ -36,6 +36,22 @@ TRAIN_FLOP_PER_RAY = 879869952
 TRAIN_RAYS = 1024
 
 
+def measured_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        for k in ("hbm_gbs_sustained", "hbm_gbs", "hbm_gbps"):
+            if k in d:
+                return float(d[k]), "measured"
+    return 6500.0, "fallback"
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch (the fine-net launch of each class), from the committed
+# ncu --set full captures: profiles/mlp_r1c_metrics.txt (render) and profiles/train_r1d_metrics.txt (training step)
+NCU_TRAFFIC_BYTES = {"render": {"fwd": 54.67e6 + 146.98e6},
+                     "train": {"fwd": 0.0021e9 + 1.0045e9, "dgrad": 0.0596e9 + 0.9499e9, "wgrad": 1.9247e9 + 0.0039e9}}
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -329,13 +345,27 @@ def main():
             if n_k > 0 and ms_k > 0:
                 kernels[k] = {"kernel": names[k], "ms_total": ms_k, "launches": n_k, "avg_launch_ms": ms_k / n_k,
                               "achieved_tflops": flops[k] / (ms_k / 1e3) / 1e12, "share_of_step": ms_k / total_ms}
+        if "wgrad" in kernels:
+            # wgrad is HBM-bound: its algorithmic bytes are every arena block it needs, once (tc_arena.cuh: fine net 38 dZ +
+            # 36 X + PE + PE(dir) blocks, coarse net 32 + 28 + PE, 16 KB each per 128-row tile)
+            wg_bytes = args.steps * 16384.0 * (76 * n_f + 61 * n_c) / 128
+            kernels["wgrad"]["achieved_gbs"] = wg_bytes / (kernels["wgrad"]["ms_total"] / 1e3) / 1e9
         top = max(kernels, key=lambda k: kernels[k]["ms_total"])
-        achieved = kernels[top]["achieved_tflops"]
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_sus, "unit": "TFLOP/s", "frac": achieved / peak_sus,
-                    "traffic": None, "kernel": names[top], "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst),
-                    "launches_timed": kernels[top]["launches"], "avg_launch_ms": kernels[top]["avg_launch_ms"],
-                    "share_of_step": kernels[top]["share_of_step"], "kernels": kernels,
-                    "step_tflops": rays_per_step_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12}
+        traffic = NCU_TRAFFIC_BYTES[args.mode].get(top)
+        if top == "wgrad":
+            hbm_peak, hbm_kind = measured_hbm()
+            achieved = kernels[top]["achieved_gbs"]
+            roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                        "traffic": traffic, "kernel": names[top], "peak_kind": "%s HBM copy bandwidth" % hbm_kind}
+        else:
+            achieved = kernels[top]["achieved_tflops"]
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_sus, "unit": "TFLOP/s", "frac": achieved / peak_sus,
+                        "traffic": traffic, "kernel": names[top],
+                        "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst)}
+        roofline.update({"traffic_unit": "bytes per launch (ncu dram read + write, fine-net launch)",
+                         "launches_timed": kernels[top]["launches"], "avg_launch_ms": kernels[top]["avg_launch_ms"],
+                         "share_of_step": kernels[top]["share_of_step"], "kernels": kernels,
+                         "step_tflops": rays_per_step_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12})
 
     line = {
         "metric": "rays/sec %s (lego 800x800, 64+128 samples)" % args.mode, "value": value, "unit": "rays/s",
