@@ -177,7 +177,11 @@ def workload_config(args, world):
         return {"workload": "lego.yaml training, %d rays/rank/step, synthetic rays+RGB, fwd+bwd+allreduce+clip/Adam" % TRAIN_RAYS,
                 "n_samples": N_SAMPLES, "n_importance": N_IMPORTANCE, "rays_per_rank": TRAIN_RAYS,
                 "parallelism": "dp%d" % world, "l2": "flushed between timed steps (256 MiB write)"}
-    return {"workload": "lego.yaml full 800x800 synthetic-camera render, 64+128 samples, bf16 MLP (BASELINE configs[1])",
+    extra = ""
+    if args.fast_sampling is not None:
+        extra = " + fast_sampling (ESS/ERT, weights_threshold %g, masked samples skipped)%s [secondary variant]" % (
+            args.fast_sampling, ", fog weights" if args.fog else "")
+    return {"workload": "lego.yaml full 800x800 synthetic-camera render, 64+128 samples, bf16 MLP (BASELINE configs[1])" + extra,
             "H": H, "W": W, "n_samples": N_SAMPLES, "n_importance": N_IMPORTANCE, "white_bkgd": True, "perturb": 0,
             "rays_per_gpu_per_step": H * W, "views_per_step": world,
             "parallelism": "image row bands over %d GPU(s), no collective" % world,
@@ -194,6 +198,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default=None, choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    # secondary (non-headline) render variant: the reference's fast_sampling (ESS/ERT) knob with this weights_threshold;
+    # --fog adds +1 to alpha_linear.bias (sigma ~ 1) so that the mask keeps a realistic share of the fine samples
+    ap.add_argument("--fast-sampling", type=float, default=None, metavar="WEIGHTS_THRESHOLD")
+    ap.add_argument("--fog", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -224,9 +232,16 @@ def main():
     from nerf_replication_b200.trainer import FusedTrainer, shard_range
 
     cfg = C.default_cfg()
+    if args.fast_sampling is not None:
+        cfg.fast_sampling, cfg.weights_threshold = True, args.fast_sampling
     precision = args.precision or "bf16"
     torch.manual_seed(0)
-    net = Network(cfg=cfg, precision=precision).cuda()
+    net = Network(cfg=cfg, precision=precision)
+    if args.fog:
+        with torch.no_grad():
+            net.model.alpha_linear.bias += 1.0
+            net.model_fine.alpha_linear.bias += 1.0
+    net = net.cuda()
     renderer = Renderer(net, cfg=cfg)
     eng = renderer._engine()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -332,7 +347,7 @@ def main():
     peak_sus, peak_burst, peak_kind = measured_peaks()
     roofline = None
     fwd_name = "mlp_tc_forward_kernel" if os.environ.get("NERF_TC_VARIANT") == "1" else "mlp_tc2_forward_kernel (CTA pair, tcgen05 cta_group::2)"
-    if precision == "bf16" and mlp_launches > 0 and mlp_ms > 0:
+    if precision == "bf16" and mlp_launches > 0 and mlp_ms > 0 and args.fast_sampling is None:   # rows actually evaluated are only known on the device when fast_sampling skips rows
         # algorithmic FLOPs per class: forward 1 186 816 / row; backward per row: fine dgrad 2*(593408-3456),
         # fine wgrad 2*593408, coarse (sigma-only) dgrad 2*459008, coarse wgrad 2*491264
         n_c, n_f = rays_per_step_local * N_SAMPLES, rays_per_step_local * (N_SAMPLES + N_IMPORTANCE)

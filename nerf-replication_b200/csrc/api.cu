@@ -303,9 +303,19 @@ static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n
       char nb[32]; snprintf(nb, 32, "r%d.prune", slot);
       if ((rc = h->buf(nb, (size_t)n * Nt, &prune_mask))) return rc;
     }
+    // fast_sampling == 2 (bf16 tensor-core path): masked rows are not evaluated at all -- sample_pdf also emits the
+    // compacted list of valid rows, raw_f is zero-filled and the fine MLP pass walks the list (same results as the mask)
+    int32_t *row_list = nullptr, *row_count = nullptr;
+    if (c.fast_sampling == 2 && c.precision == NERF_PRECISION_BF16 && h->tc_variant != 1) {
+      char nb[2][32]; snprintf(nb[0], 32, "r%d.rows", slot); snprintf(nb[1], 32, "r%d.nrows", slot);
+      if ((rc = h->buf(nb[0], (size_t)n * Nt, &row_list)) || (rc = h->buf(nb[1], 1, &row_count))) return rc;
+      NERF_CUDA_TRY(h, cudaMemsetAsync(row_count, 0, sizeof(int32_t), st));
+      NERF_CUDA_TRY(h, cudaMemsetAsync(tp.raw_f, 0, (size_t)n * Nt * 4 * sizeof(float), st));
+    }
     if ((rc = launch_sample_pdf(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? u : nullptr, tu && !u, call_id, nullptr, nullptr, nullptr,
-                                nullptr, nullptr, nullptr, tp.t_s, tp.sort_idx, st, c.weights_threshold, nullptr, prune_mask))) return rc;
-    src.t = tp.t_s; src.S = Nt; src.mask = prune_mask;
+                                nullptr, nullptr, nullptr, tp.t_s, tp.sort_idx, st, c.weights_threshold, nullptr, prune_mask,
+                                row_list, row_count))) return rc;
+    src.t = tp.t_s; src.S = Nt; src.mask = row_list ? nullptr : prune_mask; src.row_list = row_list; src.row_count = row_count;
     if ((rc = run_mlp(h, NERF_NET_FINE, src, tp.raw_f, keep, st))) return rc;
     launch_composite(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
     if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)

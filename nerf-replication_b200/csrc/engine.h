@@ -89,7 +89,8 @@ int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64
                       const float* u, bool philox_u, uint64_t call_id, const float* cdf_in, float* t_fine,
                       int64_t* inds, int64_t* below, int64_t* above, float* cdf_out, float* t_sorted,
                       int32_t* sort_idx, cudaStream_t st, float prune_w_thr = 0.25f, uint8_t* valid_fine = nullptr,
-                      uint8_t* mask_sorted = nullptr);     // a-M: ESS/ERT mask outputs (either non-NULL turns it on)
+                      uint8_t* mask_sorted = nullptr,      // a-M: ESS/ERT mask outputs (either non-NULL turns it on)
+                      int32_t* row_list = nullptr, int32_t* row_count = nullptr);   // + compacted list of the valid sorted rows
 // backward stages
 void launch_mse_grad(NerfEngine* h, const float* rgb, const float* gt, int64_t n, float scale,
                      float* d_rgb, float* loss, cudaStream_t st);
@@ -112,6 +113,10 @@ struct RowSrc {
   const float* rays_d = nullptr;    // [R,3]
   const float* t = nullptr;         // [R,S]
   const uint8_t* mask = nullptr;    // [R,S] or NULL
+  // optional compacted row list (fast_sampling work skipping, CTA-pair forward only): the kernel evaluates rows
+  // row_list[0 .. *row_count) instead of all R*S rows; both live in device memory (no host round trip)
+  const int32_t* row_list = nullptr;
+  const int32_t* row_count = nullptr;
   int64_t R = 0;
   int S = 0;
 };

@@ -230,6 +230,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
                        const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
+  if (!SAVE && src.row_count) {      // compacted row list (fast_sampling work skipping): the row count lives on the device
+    M = min((int64_t)__ldg(src.row_count), M);
+    n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
+  }
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
@@ -361,8 +365,9 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     };
     uint32_t lc = 0;
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {
-      const int64_t g = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
-      const bool valid = g < M;
+      const int64_t gl = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
+      const bool valid = gl < M;
+      const int64_t g = (!SAVE && src.row_list && valid) ? (int64_t)__ldg(src.row_list + gl) : gl;
       // training forward: this row's slice of the tile's arena blocks / bit-mask records (tc_arena.cuh)
       uint8_t* tile_base = SAVE ? act_arena + (size_t)((st * 2 + rank) * 2 + tile) * arena::act_tile_bytes() : nullptr;
       uint8_t* grow0 = SAVE ? tile_base + arena::cm_row_offset(row) : nullptr;

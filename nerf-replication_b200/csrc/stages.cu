@@ -199,7 +199,7 @@ static inline int next_pow2(int v) { int p = 32; while (p < v) p <<= 1; return p
 // prune != nullptr (a-M, volume_renderer.py:116-133,158-165): flags[k] bit 0 = coarse bin k is "empty" (w < w_thr),
 // bit 1 = the transmittance fell below ert_thr at or before bin k (prefix OR = the reference's cummax); ray_stats
 // receives (sum sigma, max sigma).
-struct PruneArgs { int on; float w_thr, ert_thr; uint8_t* valid_fine; uint8_t* mask_sorted; };
+struct PruneArgs { int on; float w_thr, ert_thr; uint8_t* valid_fine; uint8_t* mask_sorted; int32_t* row_list; int32_t* row_count; };
 __device__ __forceinline__ float build_cdf(const float4* __restrict__ raw_c, const float* __restrict__ t_c,
                                            const float* __restrict__ cdf_in, int Nc, int lane,
                                            float* tc, float* cdf, float* wtmp, const PruneArgs* prune = nullptr,
@@ -346,13 +346,33 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
     }
     for (int k = Nt + lane; k < Npad; k += 32) { s.keys[k] = __int_as_float(0x7f800000); s.kidx[k] = 0x7fffffff; }
     __syncwarp();
-    if (t_sorted || sort_idx || (prune.on && prune.mask_sorted)) {
+    if (t_sorted || sort_idx || (prune.on && (prune.mask_sorted || prune.row_list))) {
       warp_bitonic_sort(s.keys, s.kidx, Npad, lane);
       for (int k = lane; k < Nt; k += 32) {
         if (t_sorted) t_sorted[ray * Nt + k] = s.keys[k];
         if (sort_idx) sort_idx[ray * Nt + k] = s.kidx[k];
         // coarse samples stay valid; fine samples carry their flag through the same permutation (:359-370)
         if (prune.on && prune.mask_sorted) prune.mask_sorted[ray * Nt + k] = s.kidx[k] < Nc ? 1 : (uint8_t)s.fvalid[s.kidx[k] - Nc];
+      }
+      if (prune.on && prune.row_list) {
+        // work skipping: append this ray's valid rows (sorted order) to the compacted row list the fine MLP pass walks;
+        // one global atomic per ray reserves the segment
+        int total = 0;
+        for (int k0 = 0; k0 < Nt; k0 += 32) {
+          const int k = k0 + lane;
+          const bool v = k < Nt && (s.kidx[k] < Nc || s.fvalid[s.kidx[k] - Nc] != 0);
+          total += __popc(__ballot_sync(0xffffffffu, v));
+        }
+        int base = 0;
+        if (lane == 0) base = atomicAdd(prune.row_count, total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (int k0 = 0; k0 < Nt; k0 += 32) {
+          const int k = k0 + lane;
+          const bool v = k < Nt && (s.kidx[k] < Nc || s.fvalid[s.kidx[k] - Nc] != 0);
+          const unsigned b = __ballot_sync(0xffffffffu, v);
+          if (v) prune.row_list[base + __popc(b & ((1u << lane) - 1u))] = (int32_t)(ray * Nt + k);
+          base += __popc(b);
+        }
       }
     }
     __syncwarp();
@@ -362,13 +382,15 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
 int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                       const float* u, bool philox_u, uint64_t call_id, const float* cdf_in, float* t_fine,
                       int64_t* inds, int64_t* below, int64_t* above, float* cdf_out, float* t_sorted,
-                      int32_t* sort_idx, cudaStream_t st, float prune_w_thr, uint8_t* valid_fine, uint8_t* mask_sorted) {
+                      int32_t* sort_idx, cudaStream_t st, float prune_w_thr, uint8_t* valid_fine, uint8_t* mask_sorted,
+                      int32_t* row_list, int32_t* row_count) {
   if (Nc < 4 || Nf < 1 || Nc + Nf > 4096) return h->fail(NERF_E_INVALID, "sample_pdf: need Nc>=4, Nf>=1, Nc+Nf<=4096");
   if (n <= 0) return NERF_OK;
   const int Npad = next_pow2(Nc + Nf);
   PruneArgs prune;
   prune.on = (valid_fine || mask_sorted) ? 1 : 0; prune.w_thr = prune_w_thr; prune.ert_thr = 0.45f;   // ert_threshold default (:98)
-  prune.valid_fine = valid_fine; prune.mask_sorted = mask_sorted;
+  prune.valid_fine = valid_fine; prune.mask_sorted = mask_sorted; prune.row_list = row_list; prune.row_count = row_count;
+  if (row_list && (int64_t)n * (Nc + Nf) >= (int64_t)1 << 31) return h->fail(NERF_E_INVALID, "sample_pdf: row list needs n*(Nc+Nf) < 2^31");
   const size_t smem = (size_t)kWarpsPerBlock * pdf_smem_words(Nc, Nf, Npad) * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(sample_pdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   sample_pdf_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(

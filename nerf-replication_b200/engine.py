@@ -56,7 +56,7 @@ class Engine:
         c.white_bkgd, c.perturb, c.train_u = int(bool(white_bkgd)), int(bool(perturb)), int(bool(train_u))
         c.precision = {"bf16": L.PRECISION_BF16, "fp32": L.PRECISION_FP32}[precision]
         c.t_near, c.t_far, c.seed = float(t_near), float(t_far), int(seed)
-        c.fast_sampling, c.weights_threshold = int(bool(fast_sampling)), float(weights_threshold)
+        c.fast_sampling, c.weights_threshold = int(fast_sampling), float(weights_threshold)     # 0 off, 1 mask, 2 skip masked rows
 
     @property
     def precision(self):

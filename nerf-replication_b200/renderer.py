@@ -58,7 +58,7 @@ class Renderer:
 
     def _engine(self):
         return self.net.engine(n_samples=self.N_samples, n_importance=self.N_importance, white_bkgd=self.white_bkgd,
-                               perturb=self.perturb, train_u=(self.task == "train"), fast_sampling=self.fast_sampling,
+                               perturb=self.perturb, train_u=(self.task == "train"), fast_sampling=2 if self.fast_sampling else 0,
                                weights_threshold=float(self.weights_threshold))
 
     def render(self, batch, return_dict=None, jitter=None, u=None):

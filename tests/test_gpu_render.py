@@ -195,3 +195,42 @@ def test_fast_sampling_refused_by_fused_training(oracle):
     with pytest.raises(Exception, match="render path only"):
         eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad)
     eng.close()
+
+
+@pytest.mark.parametrize("case", sorted(FAST_CASES))
+def test_fast_sampling_work_skipping_equals_mask(oracle, case):
+    """fast_sampling = 2 (bf16 path): sample_pdf emits the compacted list of valid rows and the fine pass evaluates only
+    those -- the maps must equal the mask mode (= the reference's behaviour) bit for bit."""
+    from test_oracle import fast_state_dict
+    g = load_golden(case)
+    kind, thr = FAST_CASES[case]
+    eng = make_engine(oracle, oracle.round_weights_bf16(fast_state_dict(oracle, kind)), "bf16", fast_sampling=1, weights_threshold=thr)
+    o, d = dev(g["rays_o"]), dev(g["rays_d"])
+    masked = eng.render_rays(o, d, full=True)
+    eng.configure(fast_sampling=2)
+    skipped = eng.render_rays(o, d, full=True)
+    torch.cuda.synchronize()
+    for k in ("rgb", "depth", "acc"):
+        assert torch.equal(masked[k], skipped[k]), k
+    # and both sit within the bf16 gate of the reference's fast_sampling run wherever the mask agrees with it
+    d_rgb = (skipped["rgb"].cpu() - torch.from_numpy(g["rgb_map"])).abs().max(dim=1).values
+    print(case, "rays over 1e-3 vs fp32 reference:", int((d_rgb > BF16_RGB_TOL).sum()), "max", float(d_rgb.max()))
+    eng.close()
+
+
+def test_fast_sampling_work_skipping_full_size(oracle):
+    """BASELINE-size band (800 x 40 rays): compacted evaluation == masked evaluation, and the unpruned render differs."""
+    sd = oracle.round_weights_bf16(oracle.fog_state_dict(0))
+    eng = make_engine(oracle, sd, "bf16", fast_sampling=1, weights_threshold=0.02)
+    c2w = oracle.lego_pose(0)
+    pix = np.arange(800 * 380, 800 * 420).astype(np.int64)
+    o, d = (torch.from_numpy(x).cuda() for x in oracle.get_rays_np(c2w, 800, 800, pix))
+    masked = eng.render_rays(o, d)
+    eng.configure(fast_sampling=2)
+    skipped = eng.render_rays(o, d)
+    eng.configure(fast_sampling=0)
+    plain = eng.render_rays(o, d)
+    torch.cuda.synchronize()
+    assert torch.equal(masked["rgb"], skipped["rgb"]) and torch.equal(masked["depth"], skipped["depth"])
+    assert maxabs(plain["rgb"], skipped["rgb"]) > 1e-5
+    eng.close()
