@@ -307,7 +307,8 @@ static unsigned int g_debug_host[8];
 int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st) {
   const int64_t M = src.R * src.S;
   if (M <= 0) return NERF_OK;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};          // the opt-in shared-memory size is a per-device function attribute
+  bool& attr_set = attr_set_dev[h->device & 63];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(mlp_tc_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc smem attribute: ") + cudaGetErrorString(e));

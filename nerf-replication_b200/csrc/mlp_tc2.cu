@@ -418,7 +418,8 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   using namespace v2;
   const int64_t M = src.R * src.S;
   if (M <= 0) return NERF_OK;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};          // the opt-in shared-memory size is a per-device function attribute
+  bool& attr_set = attr_set_dev[h->device & 63];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(mlp_tc2_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_tc2_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);

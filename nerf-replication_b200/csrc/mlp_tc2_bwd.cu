@@ -431,7 +431,8 @@ int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const fl
   using namespace bw;
   const int64_t M = src.R * src.S;
   if (M <= 0) return NERF_OK;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};          // the opt-in shared-memory size is a per-device function attribute
+  bool& attr_set = attr_set_dev[h->device & 63];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(mlp_tc2_dgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_tc2_dgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
@@ -765,7 +766,8 @@ int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const
                   float* flat_grad_net, cudaStream_t st) {
   using namespace wg;
   if (M <= 0) return NERF_OK;
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {};          // the opt-in shared-memory size is a per-device function attribute
+  bool& attr_set = attr_set_dev[h->device & 63];
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(mlp_tc2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_wgrad smem attribute: ") + cudaGetErrorString(e));

@@ -1,4 +1,4 @@
-"""Where do the CTA-pair kernels wait?  python scratch/waitprof.py  (GPU box)"""
+"""Where do the CTA-pair kernels wait?  python profiles/waitprof.py  (GPU box)"""
 import sys, torch
 sys.path.insert(0, "."); sys.path.insert(0, "tests")
 
