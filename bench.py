@@ -163,7 +163,7 @@ def run_reference(args, rank):
     v = chunk * args.steps / dt
     sample = "%d-ray slices of the 800x800 C2 view per step (oracle/nerf_oracle.py, CPU fp32 torch)" % chunk
     print(json.dumps({
-        "impl": "reference", "metric": "rays/sec render (lego 800x800, 64+128 samples)", "value": v, "unit": "rays/s",
+        "impl": "reference", "metric": "rays/sec %s (lego 800x800, 64+128 samples)" % args.mode, "value": v, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, 1),
