@@ -159,6 +159,41 @@ int nerf_train_backward(NerfEngine* h, const float* rays_o, const float* rays_d,
 int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* flat_grad, float* m, float* v,
                    float lr, float beta1, float beta2, float eps, float clip, int step, void* stream);
 
+/* ---- either side of the path, on the device -------------------------------- */
+/* Ray bank = Dataset of src/datasets/nerf/blender.py:8-170 resident in HBM: all views' images (fp32 0..255 as the
+ * reference keeps them after cv2.resize, :50-52; storage 1 = uint8 when the pixel values are integral) and poses
+ * (transform_matrix rows 0..2, 12 doubles).  focal/cx/cy as blender.py:102-103.  Several banks (train / val / test
+ * splits) may live in one handle; nerf_destroy frees them all. */
+int nerf_bank_create(NerfEngine* h, int n_views, int H, int W, double focal, double cx, double cy, int storage,
+                     int* bank_out);
+int nerf_bank_destroy(NerfEngine* h, int bank);
+/* image_host: [H,W,3] fp32 (storage 0) or uint8 (storage 1); c2w_host: 12 doubles.  Synchronous on return. */
+int nerf_bank_set_view(NerfEngine* h, int bank, int view, const void* image_host, const double* c2w_host, void* stream);
+/* Dataset.__getitem__ (blender.py:84-170) for n pixels of `view`: rays_o/rays_d [n,3] (float64 camera math rounded
+ * to fp32), colors [n,3] = image[v,u]/255, ids_out [n] int64 (any output may be NULL).  mode 0: pixel_ids (device
+ * int64[n], e.g. the caller's np.random.choice, :108-110); mode 1: the row-major range [pix0, pix0+n) (val/test
+ * branch, :112-115); mode 2: n distinct pixels drawn on the device -- ids[i] = P(i) for a bijection P of [0,H*W) keyed
+ * by (NerfConfig.seed, draw). */
+int nerf_bank_sample(NerfEngine* h, int bank, int view, int mode, const int64_t* pixel_ids, int64_t pix0, uint64_t draw,
+                     int64_t n, float* rays_o, float* rays_d, float* colors, int64_t* ids_out, void* stream);
+/* the same bijection on the host (checker for mode 2; no CUDA call) */
+int nerf_bank_permutation_host(uint64_t seed, uint64_t draw, int64_t n_pix, int64_t n, int64_t* ids_out);
+/* nerf_bank_sample + nerf_forward_backward in one call: a training step whose only host input is (view, draw). */
+int nerf_bank_train_step(NerfEngine* h, int bank, int view, int mode, const int64_t* pixel_ids, int64_t pix0, uint64_t draw,
+                         int64_t n, const float* jitter, const float* u, float grad_scale, float* loss, float* flat_grad,
+                         float* rgb_out, void* stream);
+/* Evaluator sums, src/evaluators/nerf.py:23-30,96-103, over n_elems floats of rgb_pred / rgb_gt:
+ * *sse_out (device double) = sum of fp32 (clip(pred,0,1)-clip(gt,0,1))^2 -> mse = sse/n_elems (:101);
+ * *sq8_out (device uint64) = sum of psnr_metric's uint8 terms, ((p8-g8) mod 256)^2 mod 256 with x8 = trunc(clip(x)*255)
+ * (numpy uint8 arithmetic wraps, :24-26) -> mse8 = sq8/n_elems, psnr = 100 if mse8 < 1e-10 else 10 log10(255^2/mse8). */
+int nerf_eval_image(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int64_t n_elems, double* sse_out,
+                    unsigned long long* sq8_out, void* stream);
+/* ssim_metric, src/evaluators/nerf.py:52-77 = skimage.metrics.structural_similarity(uint8 pred, uint8 gt, win_size,
+ * channel_axis=2) on x8 = trunc(clip(x,0,1)*255) of [H,W,3] images: *ssim_sum_out (device double) = sum of the SSIM map
+ * over its border-cropped (H-win+1)x(W-win+1) region and the 3 channels; ssim = sum / (3 (H-win+1)(W-win+1)). */
+int nerf_eval_ssim(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int H, int W, int win_size, double* ssim_sum_out,
+                   void* stream);
+
 /* ---- debug / bring-up ------------------------------------------------------------------------------ */
 /* tcgen05 descriptor probe battery (see csrc/probe.cu); writes results for `variant` into out[]. */
 int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K,

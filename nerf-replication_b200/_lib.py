@@ -53,6 +53,14 @@ SIGNATURES = {
     "nerf_train_forward": (_I, [_P, _P, _P, _L, _P, _P, _P, _P, _P]),
     "nerf_train_backward": (_I, [_P, _P, _P, _L, _P, _P, _P, _I, _P]),
     "nerf_clip_adam": (_I, [_P, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I, _P]),
+    "nerf_bank_create": (_I, [_P, _I, _I, _I, _D, _D, _D, _I, C.POINTER(_I)]),
+    "nerf_bank_destroy": (_I, [_P, _I]),
+    "nerf_bank_set_view": (_I, [_P, _I, _I, _P, C.POINTER(_D), _P]),
+    "nerf_bank_sample": (_I, [_P, _I, _I, _I, _P, _L, C.c_uint64, _L, _P, _P, _P, _P, _P]),
+    "nerf_bank_permutation_host": (_I, [C.c_uint64, C.c_uint64, _L, _L, _P]),
+    "nerf_bank_train_step": (_I, [_P, _I, _I, _I, _P, _L, C.c_uint64, _L, _P, _P, _F, _P, _P, _P, _P]),
+    "nerf_eval_image": (_I, [_P, _P, _P, _L, _P, _P, _P]),
+    "nerf_eval_ssim": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
     "nerf_debug_umma_probe": (_I, [_I, _P, _P, _P, _I, _I, _I, _P]),
     "nerf_debug_tc_watchdog": (_I, [C.POINTER(C.c_uint)]),
     "nerf_debug_waitprof": (_I, [_I, C.POINTER(C.c_ulonglong)]),

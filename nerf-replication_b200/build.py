@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libnerf_b200.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "stages.cu", "mlp_fp32.cu", "mlp_tc.cu", "mlp_tc2.cu", "mlp_tc2_bwd.cu", "adam.cu", "probe.cu"]
+SOURCES = ["api.cu", "stages.cu", "mlp_fp32.cu", "mlp_tc.cu", "mlp_tc2.cu", "mlp_tc2_bwd.cu", "adam.cu", "bank.cu", "probe.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-Wno-deprecated-gpu-targets", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -76,6 +76,7 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
+  for (auto& b : h->banks) { if (b.images) cudaFree(b.images); if (b.poses) cudaFree(b.poses); }
   if (h->wpack) cudaFree(h->wpack);
   if (h->wpack_bwd) cudaFree(h->wpack_bwd);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);

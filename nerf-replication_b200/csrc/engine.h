@@ -23,6 +23,11 @@ struct NerfEngine {
   struct Buf { void* p = nullptr; size_t bytes = 0; };
   std::map<std::string, Buf> ws;
 
+  // ray banks (bank.cu): every view's image and pose resident in HBM
+  struct Bank { void* images = nullptr; double* poses = nullptr; int V = 0, H = 0, W = 0; double focal = 0, cx = 0, cy = 0;
+                int storage = 0; std::vector<uint8_t> loaded; };
+  std::vector<Bank> banks;
+
   // taps of the last training forward (nerf_train_forward), consumed by nerf_train_backward
   struct Taps { float *t_c = nullptr, *raw_c = nullptr, *t_s = nullptr, *raw_f = nullptr; int32_t* sort_idx = nullptr;
                 uint64_t call_id = 0; int64_t n = -1; const float *jitter = nullptr, *u = nullptr; } taps;

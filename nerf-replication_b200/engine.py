@@ -266,6 +266,74 @@ class Engine:
                                             self._p(m, name="m"), self._p(v, name="v"), lr, beta1, beta2, eps, clip, int(step),
                                             self._stream()))
 
+    # -- ray bank + evaluator sums (csrc/bank.cu) ------------------------------------
+    def bank_create(self, n_views, H, W, focal, cx=None, cy=None, uint8=False):
+        bank = C.c_int(-1)
+        self._check(self.lib.nerf_bank_create(self.h, int(n_views), int(H), int(W), float(focal), W / 2 if cx is None else cx,
+                                              H / 2 if cy is None else cy, int(bool(uint8)), C.byref(bank)))
+        return bank.value
+
+    def bank_destroy(self, bank):
+        self._check(self.lib.nerf_bank_destroy(self.h, int(bank)))
+
+    def bank_set_view(self, bank, view, image, c2w):
+        """image: contiguous host array [H,W,3], float32 (0..255) or uint8 to match the bank; c2w: 4x4 or 3x4."""
+        c2w = [float(x) for row in c2w[:3] for x in row[:4]]
+        self._check(self.lib.nerf_bank_set_view(self.h, int(bank), int(view), image.ctypes.data, (C.c_double * 12)(*c2w),
+                                                self._stream()))
+
+    _BANK_MODES = {"ids": 0, "range": 1, "random": 2}
+
+    def bank_sample(self, bank, view, n, mode="random", pixel_ids=None, pix0=0, draw=0, want_ids=False):
+        """Dataset.__getitem__ on the device -> dict(rays_o, rays_d, colors[, ids])."""
+        dev = "cuda:%d" % self.device
+        o, d, c = torch.empty(n, 3, device=dev), torch.empty(n, 3, device=dev), torch.empty(n, 3, device=dev)
+        ids = torch.empty(n, dtype=torch.int64, device=dev) if want_ids else None
+        self._check(self.lib.nerf_bank_sample(self.h, int(bank), int(view), self._BANK_MODES[mode],
+                                              self._p(pixel_ids, torch.int64, "pixel_ids"), int(pix0), int(draw), int(n),
+                                              o.data_ptr(), d.data_ptr(), c.data_ptr(), None if ids is None else ids.data_ptr(),
+                                              self._stream()))
+        out = {"rays_o": o, "rays_d": d, "colors": c}
+        if want_ids:
+            out["ids"] = ids
+        return out
+
+    def bank_permutation_host(self, seed, draw, n_pix, n):
+        import numpy as np
+        ids = np.empty(n, dtype=np.int64)
+        rc = self.lib.nerf_bank_permutation_host(int(seed), int(draw), int(n_pix), int(n), ids.ctypes.data)
+        if rc != 0:
+            raise EngineError("nerf_bank_permutation_host: bad argument")
+        return ids
+
+    def bank_train_step(self, bank, view, n, flat_grad, mode="random", pixel_ids=None, pix0=0, draw=0, jitter=None, u=None,
+                        grad_scale=1.0, loss=None):
+        loss = torch.empty((), device="cuda:%d" % self.device) if loss is None else loss
+        self._check(self.lib.nerf_bank_train_step(self.h, int(bank), int(view), self._BANK_MODES[mode],
+                                                  self._p(pixel_ids, torch.int64, "pixel_ids"), int(pix0), int(draw), int(n),
+                                                  self._p(jitter, name="jitter"), self._p(u, name="u"), float(grad_scale),
+                                                  loss.data_ptr(), self._p(flat_grad, name="flat_grad"), None, self._stream()))
+        return loss
+
+    def eval_image(self, rgb_pred, rgb_gt):
+        """-> device tensors (sse float64 [], sq8 int64 []) of src/evaluators/nerf.py:23-30,96-103 (see nerf_eval_image)."""
+        if rgb_pred.numel() != rgb_gt.numel():
+            raise EngineError("eval_image: rgb_pred and rgb_gt differ in size")
+        dev = "cuda:%d" % self.device
+        sse, sq8 = torch.empty((), dtype=torch.float64, device=dev), torch.empty((), dtype=torch.int64, device=dev)
+        self._check(self.lib.nerf_eval_image(self.h, self._p(rgb_pred, name="rgb_pred"), self._p(rgb_gt, name="rgb_gt"),
+                                             rgb_pred.numel(), sse.data_ptr(), sq8.data_ptr(), self._stream()))
+        return sse, sq8
+
+    def eval_ssim(self, rgb_pred, rgb_gt, H, W, win_size=7):
+        """-> device float64 []: mean SSIM as src/evaluators/nerf.py:71-77 computes it (see nerf_eval_ssim)."""
+        if rgb_pred.numel() != H * W * 3 or rgb_gt.numel() != H * W * 3:
+            raise EngineError("eval_ssim takes [H,W,3] images")
+        s = torch.empty((), dtype=torch.float64, device="cuda:%d" % self.device)
+        self._check(self.lib.nerf_eval_ssim(self.h, self._p(rgb_pred, name="rgb_pred"), self._p(rgb_gt, name="rgb_gt"), int(H), int(W),
+                                            int(win_size), s.data_ptr(), self._stream()))
+        return s / (3 * (H - win_size + 1) * (W - win_size + 1))
+
     # -- debug ----------------------------------------------------------------------------------
     def umma_probe(self, variant, a, b):
         if variant >= 4:                       # MN-major operands: a = At [K, 128], b = Bt [K, N]
