@@ -339,6 +339,37 @@ def main():
     clocks = sampler.finish()
     ms_e2e, _ = timed(step_e2e, False)
 
+    bank_loop = None
+    if args.mode == "train":
+        # the same step driven by Trainer.train from images resident in HBM (ray bank): the pixel draw,
+        # ray generation and colour gather run on the device, so a step has no host input at all; one loss read at the end
+        import numpy as np
+        from nerf_replication_b200.dataset import Dataset
+        from nerf_replication_b200.optimizer import FusedAdam
+        from nerf_replication_b200.trainer import Recorder, Trainer, make_data_loader
+        n_views = 8
+        imgs = np.random.RandomState(rank).randint(0, 256, size=(n_views, H, W, 3), dtype=np.uint8)
+        poses = np.stack([O.lego_pose(v, n_views) for v in range(n_views)])
+        ds = Dataset(net=net, images=imgs, transform_matrices=poses, camera_angle_x=O.CAMERA_ANGLE_X, split="train", seed=rank,
+                     n_rays=TRAIN_RAYS)
+        opt = FusedAdam(net, lr=5e-4, eps=1e-8, clip=40.0)
+        opt.m, opt.v, opt.step_count = trainer.m, trainer.v, trainer.step_count      # continue the same optimisation state
+        opt._bind_state()
+        drv = Trainer(net, cfg, log_interval=10 ** 9, verbose=False)
+        drv.train(0, make_data_loader(cfg, ds, True, world > 1, args.warmup, rank, world), opt, Recorder())
+        barrier()
+        t0 = time.perf_counter()
+        losses = drv.train(1, make_data_loader(cfg, ds, True, world > 1, args.steps, rank, world), opt, Recorder())
+        last_loss = float(losses[-1])
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        bank_loop = {"value": TRAIN_RAYS * world * args.steps / float(dt), "unit": "rays/s", "ms_per_step": 1e3 * float(dt) / args.steps,
+                     "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4.0 / args.steps, "last_loss": last_loss,
+                     "api": "Trainer.train: nerf_bank_train_step (device pixel draw + rays + colours + fwd + loss + bwd) + "
+                            "FusedAdam.step; %d synthetic %dx%d views resident in HBM; no L2 flush between steps" % (n_views, H, W)}
+
     total_ms = sum(ms_dev)
     rays_job = rays_per_step_local * world
     value = rays_job * args.steps / (total_ms / 1e3)
@@ -396,6 +427,8 @@ def main():
         v, n_done, dt = cpu_render_rate(12.0, threads)
         line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": threads, "kind": "port",
                                 "sample": "%d rays (2048-ray slices from the centre rows of the same 800x800 view), %.1f s, oracle/nerf_oracle.py CPU fp32 torch" % (n_done, dt)}
+    if bank_loop is not None:
+        line["bank_loop"] = bank_loop
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

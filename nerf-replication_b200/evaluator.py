@@ -6,7 +6,6 @@ uniform-window SSIM (``skimage.metrics.structural_similarity``, :71-77) per view
 sums are computed by csrc/bank.cu kernels from the rendered rgb still in HBM -- the rendered image is never copied to the
 host unless ``result_dir`` asks for the PNGs the reference writes (:56-63).
 """
-import math
 import os
 
 import numpy as np
@@ -24,10 +23,10 @@ class Evaluator:
 
     @staticmethod
     def _psnr_from_sum(sq8, n):
-        mse = sq8 / n                                   # np.mean of the uint8 array (float64), nerf.py:26
+        mse = np.float64(sq8) / n                       # np.mean of the uint8 array (float64; integer sum is exact), nerf.py:26
         if mse < 1e-10:
             return 100.0
-        return 10 * math.log10((255 ** 2) / mse)        # :30
+        return float(10 * np.log10((255 ** 2) / mse))   # :30 (numpy's log10, as the reference)
 
     def psnr_metric(self, img_pred, img_gt):
         _, sq8 = self._eng().eval_image(img_pred.contiguous().float(), img_gt.contiguous().float())

@@ -208,6 +208,8 @@ class Trainer:
         for iteration, (view, draw) in enumerate(data_loader):
             data_time = time.time() - end
             eng = self.renderer._engine()
+            if eng.cfg.seed != ds.seed:
+                eng.configure(seed=ds.seed)             # the pixel draw is keyed by (dataset seed, draw)
             eng.bank_train_step(ds.bank, view, ds.n_rays, self.net.flat_grad, mode="random", draw=draw, jitter=jitter, u=u,
                                 loss=losses[iteration])
             allreduce_mean_(self.net.flat_grad)
