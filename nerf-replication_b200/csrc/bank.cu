@@ -94,7 +94,7 @@ __global__ void bank_sample_kernel(BankArgs a, int mode, const int64_t* __restri
 constexpr int kEvalThreads = 256;
 
 // Deterministic grid reduction of one double + one uint64 per thread: warp shuffle, fixed-order fold per block, then the
-// last block to finish folds the per-block partials in block order (same grid => same bits).
+// last block to finish folds the per-block partials in a fixed lane-strided order (same grid => same bits).
 __device__ __forceinline__ void grid_fold(double a, unsigned long long b, double* part_a, unsigned long long* part_b,
                                           unsigned int* done, double* out_a, unsigned long long* out_b) {
   __shared__ double s_a[kEvalThreads / 32];
@@ -116,13 +116,20 @@ __device__ __forceinline__ void grid_fold(double a, unsigned long long b, double
     s_last = atomicAdd(done, 1u) == (unsigned int)nblk - 1u;
   }
   __syncthreads();
-  if (s_last && tid == 0) {
+  if (s_last && tid < 32) {      // the last block's first warp folds the per-block partials: lane-strided, then a fixed tree
     __threadfence();
     double fa = 0.0; unsigned long long fb = 0;
-    for (int k = 0; k < nblk; ++k) { fa += ((volatile double*)part_a)[k]; fb += ((volatile unsigned long long*)part_b)[k]; }
-    *out_a = fa;
-    if (out_b) *out_b = fb;
-    *done = 0;
+    for (int k = tid; k < nblk; k += 32) { fa += __ldcg(part_a + k); fb += __ldcg(part_b + k); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      fa += __shfl_down_sync(0xffffffffu, fa, o);
+      fb += __shfl_down_sync(0xffffffffu, fb, o);
+    }
+    if (tid == 0) {
+      *out_a = fa;
+      if (out_b) *out_b = fb;
+      *done = 0;
+    }
   }
 }
 
@@ -132,15 +139,23 @@ eval_image_kernel(const float* __restrict__ pred, const float* __restrict__ gt, 
                   unsigned long long* __restrict__ sq8_out) {
   double sse = 0.0;
   unsigned long long sq8 = 0;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float p = fminf(fmaxf(pred[i], 0.f), 1.f), g = fminf(fmaxf(gt[i], 0.f), 1.f);     // np.clip(x, 0, 1), nerf.py:98-99
+  auto term = [&](float pv, float gv) {
+    const float p = fminf(fmaxf(pv, 0.f), 1.f), g = fminf(fmaxf(gv, 0.f), 1.f);            // np.clip(x, 0, 1), nerf.py:98-99
     const float d = __fsub_rn(p, g);
     sse += (double)__fmul_rn(d, d);                                                          // (pred - gt) ** 2 in fp32, :101
     // psnr_metric, nerf.py:24-26: (x * 255).astype(np.uint8) truncates; uint8 - uint8 and ** 2 wrap modulo 256
     const uint32_t pq = (uint32_t)__float2int_rz(__fmul_rn(p, 255.0f)), gq = (uint32_t)__float2int_rz(__fmul_rn(g, 255.0f));
     const uint32_t dq = (pq - gq) & 255u;
     sq8 += (dq * dq) & 255u;
+  };
+  const int64_t tid0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+  const bool vec = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt)) & 15) == 0;
+  const int64_t n4 = vec ? n / 4 : 0;
+  for (int64_t i = tid0; i < n4; i += nthr) {          // 16-byte loads; the per-thread order of terms is fixed by the grid
+    const float4 p = __ldg(reinterpret_cast<const float4*>(pred) + i), g = __ldg(reinterpret_cast<const float4*>(gt) + i);
+    term(p.x, g.x); term(p.y, g.y); term(p.z, g.z); term(p.w, g.w);
   }
+  for (int64_t i = n4 * 4 + tid0; i < n; i += nthr) term(pred[i], gt[i]);
   grid_fold(sse, sq8, part_sse, part_sq8, done, sse_out, sq8_out);
 }
 
@@ -156,18 +171,34 @@ __global__ void quantise_u8_kernel(const float* __restrict__ x, int64_t n, uint8
 __global__ void __launch_bounds__(kEvalThreads)
 ssim_kernel(const uint8_t* __restrict__ p8, const uint8_t* __restrict__ g8, int H, int W, int win, double* __restrict__ part,
             unsigned long long* __restrict__ part_n, unsigned int* __restrict__ done, double* __restrict__ out) {
-  const int x0 = blockIdx.x * blockDim.x + threadIdx.x, y0 = blockIdx.y * blockDim.y + threadIdx.y;
+  // the block's 32 x 8 outputs read a (32+win-1) x (8+win-1) pixel tile of both images: staged once in shared memory
+  extern __shared__ uint8_t s_tile[];
+  const int tw = 32 + win - 1, th = 8 + win - 1, row_bytes = tw * 3;
+  uint8_t* sp = s_tile;
+  uint8_t* sg = s_tile + th * row_bytes;
+  const int bx = blockIdx.x * 32, by = blockIdx.y * 8, tid = threadIdx.y * 32 + threadIdx.x;
+  for (int e = tid; e < th * row_bytes; e += kEvalThreads) {
+    const int ty = e / row_bytes, tb = e % row_bytes;
+    const int gy = by + ty, gxb = bx * 3 + tb;
+    const bool in = gy < H && gxb < W * 3;
+    sp[e] = in ? __ldg(p8 + (size_t)gy * W * 3 + gxb) : 0;
+    sg[e] = in ? __ldg(g8 + (size_t)gy * W * 3 + gxb) : 0;
+  }
+  __syncthreads();
+  const int x0 = bx + threadIdx.x, y0 = by + threadIdx.y;
   const int ow = W - win + 1, oh = H - win + 1;
   double acc = 0.0;
   if (x0 < ow && y0 < oh) {
     uint32_t sx[3] = {0, 0, 0}, sy[3] = {0, 0, 0}, sxx[3] = {0, 0, 0}, syy[3] = {0, 0, 0}, sxy[3] = {0, 0, 0};
     for (int dy = 0; dy < win; ++dy) {
-      const uint8_t* pr = p8 + ((size_t)(y0 + dy) * W + x0) * 3;
-      const uint8_t* gr = g8 + ((size_t)(y0 + dy) * W + x0) * 3;
-      for (int k = 0; k < win * 3; ++k) {
-        const uint32_t a = __ldg(pr + k), b = __ldg(gr + k);
-        const int c = k % 3;
-        sx[c] += a; sy[c] += b; sxx[c] += a * a; syy[c] += b * b; sxy[c] += a * b;
+      const uint8_t* pr = sp + (threadIdx.y + dy) * row_bytes + threadIdx.x * 3;
+      const uint8_t* gr = sg + (threadIdx.y + dy) * row_bytes + threadIdx.x * 3;
+      for (int dx = 0; dx < win; ++dx) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const uint32_t a = pr[dx * 3 + c], b = gr[dx * 3 + c];
+          sx[c] += a; sy[c] += b; sxx[c] += a * a; syy[c] += b * b; sxy[c] += a * b;
+        }
       }
     }
     const double np_ = (double)(win * win), cov_norm = np_ / (np_ - 1.0);
@@ -284,7 +315,7 @@ extern "C" int nerf_eval_image(NerfEngine* h, const float* rgb_pred, const float
   if (!h) return NERF_E_INVALID;
   if (!rgb_pred || !rgb_gt || n_elems <= 0 || !sse_out || !sq8_out) return h->fail(NERF_E_INVALID, "nerf_eval_image: bad argument");
   cudaSetDevice(h->device);
-  const int blocks = (int)std::min<int64_t>((n_elems + kEvalThreads - 1) / kEvalThreads, (int64_t)h->num_sms * 8);
+  const int blocks = (int)std::min<int64_t>((n_elems + kEvalThreads - 1) / kEvalThreads, (int64_t)h->num_sms * 4);
   double* part_sse; unsigned long long* part_sq8; unsigned int* done;
   int rc;
   const bool fresh = h->ws.find("eval.done") == h->ws.end();
@@ -316,7 +347,7 @@ extern "C" int nerf_eval_ssim(NerfEngine* h, const float* rgb_pred, const float*
   const int qb = (int)std::min<int64_t>((n + 255) / 256, (int64_t)h->num_sms * 8);
   quantise_u8_kernel<<<qb, 256, 0, st>>>(rgb_pred, n, p8);
   quantise_u8_kernel<<<qb, 256, 0, st>>>(rgb_gt, n, g8);
-  ssim_kernel<<<grid, block, 0, st>>>(p8, g8, H, W, win_size, part, part_n, done, ssim_sum_out);
+  ssim_kernel<<<grid, block, 2 * (8 + win_size - 1) * (32 + win_size - 1) * 3, st>>>(p8, g8, H, W, win_size, part, part_n, done, ssim_sum_out);
   h->launches += 3;
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? NERF_OK : h->fail(NERF_E_CUDA, std::string("nerf_eval_ssim: ") + cudaGetErrorString(e));

@@ -19,7 +19,12 @@ class Evaluator:
         self.result_dir = result_dir
 
     def _eng(self):
-        return self._engine if self._engine is not None else self._net.engine()
+        if self._engine is None:
+            if self._net is not None:
+                return self._net.engine()
+            from .engine import Engine          # Evaluator() as the reference's factory builds it: the sums need no weights
+            self._engine = Engine()
+        return self._engine
 
     @staticmethod
     def _psnr_from_sum(sq8, n):

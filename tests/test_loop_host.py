@@ -3,6 +3,7 @@ the reference's own Dataset.__getitem__ / samplers / ExponentialLR / Evaluator.p
 (oracle/make_golden_loop.py), and the product's host logic (view schedule, lr schedule, checkpoint layout, the keyed
 pixel bijection's host copy) against both."""
 import json
+from types import SimpleNamespace
 import os
 
 import numpy as np
@@ -222,3 +223,28 @@ def test_dataset_reads_the_blender_layout(tmp_path):
     assert np.array_equal(half._host_images[1], cv2.resize(images[1], (6, 8), interpolation=cv2.INTER_LINEAR))
     with pytest.raises(Exception):
         half.bank                                                             # not attached: no CPU path
+
+
+def test_ray_loader_gives_every_rank_its_own_views_and_pixel_draws():
+    """N > 1 without a GPU: two ranks' loaders over one epoch -- views follow the reference's DistributedSampler split, the
+    (rank, iteration) -> draw id map is injective, and a resumed loader continues the draw sequence."""
+    from nerf_replication_b200.trainer import make_data_loader
+    from nerf_replication_b200.view_schedule import distributed_pass
+    cfg = SimpleNamespace(train=SimpleNamespace(batch_size=1, shuffle=True), test=SimpleNamespace(batch_size=1))
+    ds = list(range(10))                      # the loader only needs len(dataset)
+    loaders = [make_data_loader(cfg, ds, True, True, 12, r, 2) for r in range(2)]
+    seen = set()
+    for r, ld in enumerate(loaders):
+        ld.batch_sampler.sampler.set_epoch(3)
+        items = list(ld)
+        share = distributed_pass(10, 3, r, 2)
+        assert [v for v, _ in items] == (share * 3)[:12] and len(ld) == 12
+        draws = [d for _, d in items]
+        assert draws == [i * 2 + r for i in range(12)]
+        seen |= set(draws)
+    assert len(seen) == 24
+    assert [d for _, d in loaders[1]][:2] == [25, 27]            # next epoch continues where the last one stopped
+    with pytest.raises(NotImplementedError):
+        make_data_loader(SimpleNamespace(train=SimpleNamespace(batch_size=4, shuffle=True)), ds)
+    val = make_data_loader(cfg, ds, is_train=False)
+    assert [v for v, _ in val] == list(range(10))
