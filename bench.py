@@ -163,7 +163,7 @@ def run_reference(args, rank):
     v = chunk * args.steps / dt
     sample = "%d-ray slices of the 800x800 C2 view per step (oracle/nerf_oracle.py, CPU fp32 torch)" % chunk
     print(json.dumps({
-        "impl": "reference", "metric": "rays/sec %s (lego 800x800, 64+128 samples)" % args.mode, "value": v, "unit": "rays/s",
+        "impl": "reference", "metric": "rays/sec %s (lego 800x800, %d+%d samples)" % (args.mode, N_SAMPLES, N_IMPORTANCE), "value": v, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, 1),
@@ -181,7 +181,8 @@ def workload_config(args, world):
     if args.fast_sampling is not None:
         extra = " + fast_sampling (ESS/ERT, weights_threshold %g, masked samples skipped)%s [secondary variant]" % (
             args.fast_sampling, ", fog weights" if args.fog else "")
-    return {"workload": "lego.yaml full 800x800 synthetic-camera render, 64+128 samples, bf16 MLP (BASELINE configs[1])" + extra,
+    return {"workload": ("lego.yaml full 800x800 synthetic-camera render, %d+%d samples, bf16 MLP (BASELINE configs[%d])" % (
+                N_SAMPLES, N_IMPORTANCE, 1 if (N_SAMPLES, N_IMPORTANCE) == (64, 128) else 3)) + extra,
             "H": H, "W": W, "n_samples": N_SAMPLES, "n_importance": N_IMPORTANCE, "white_bkgd": True, "perturb": 0,
             "rays_per_gpu_per_step": H * W, "views_per_step": world,
             "parallelism": "image row bands over %d GPU(s), no collective" % world,
@@ -202,7 +203,17 @@ def main():
     # --fog adds +1 to alpha_linear.bias (sigma ~ 1) so that the mask keeps a realistic share of the fine samples
     ap.add_argument("--fast-sampling", type=float, default=None, metavar="WEIGHTS_THRESHOLD")
     ap.add_argument("--fog", action="store_true")
+    # secondary configurations of BASELINE.json: configs[3] = --samples 128 256, configs[4] = --mode train --train-rays 8192
+    ap.add_argument("--samples", type=int, nargs=2, default=None, metavar=("N_SAMPLES", "N_IMPORTANCE"))
+    ap.add_argument("--train-rays", type=int, default=None)
     args = ap.parse_args()
+    global N_SAMPLES, N_IMPORTANCE, TRAIN_RAYS, TRAIN_FLOP_PER_RAY
+    if args.samples:
+        N_SAMPLES, N_IMPORTANCE = args.samples
+    if args.train_rays:
+        TRAIN_RAYS = args.train_rays
+    # forward E evals + fine backward (wgrad + dgrad) per fine eval + coarse (sigma-only) backward per coarse eval
+    TRAIN_FLOP_PER_RAY = (2 * N_SAMPLES + N_IMPORTANCE) * FLOP_PER_EVAL + (N_SAMPLES + N_IMPORTANCE) * 2366720 + N_SAMPLES * 1900544
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -234,6 +245,7 @@ def main():
     from nerf_replication_b200.trainer import FusedTrainer, shard_range
 
     cfg = C.default_cfg()
+    cfg.task_arg.N_samples, cfg.task_arg.N_importance = N_SAMPLES, N_IMPORTANCE
     if args.fast_sampling is not None:
         cfg.fast_sampling, cfg.weights_threshold = True, args.fast_sampling
     precision = args.precision or "bf16"
@@ -416,7 +428,7 @@ def main():
                          "step_tflops": rays_per_step_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12})
 
     line = {
-        "metric": "rays/sec %s (lego 800x800, 64+128 samples)" % args.mode, "value": value, "unit": "rays/s",
+        "metric": "rays/sec %s (lego 800x800, %d+%d samples)" % (args.mode, N_SAMPLES, N_IMPORTANCE), "value": value, "unit": "rays/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": precision, "data": "synthetic",
         "config": workload_config(args, world),
