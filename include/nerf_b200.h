@@ -60,7 +60,7 @@ typedef struct NerfConfig {
   uint64_t seed;         /* Philox seed for in-kernel jitter/u when no arrays given   */
   int32_t fast_sampling; /* cfg.fast_sampling  (0): ESS/ERT pruning mask on the fine pass (:116-244, :359-374);
                           * 1 = mask like the reference (masked samples evaluated, raw zeroed), 2 = same results but the
-                          * masked samples are skipped (compacted row list; bf16 path, falls back to 1 in fp32 mode)   */
+                          * masked samples are skipped (compacted row list; bf16 render path -- fp32 mode and the training calls mask)   */
   float weights_threshold; /* cfg.weights_threshold (0.25): ESS "empty bin" weight threshold (:132-133)        */
 } NerfConfig;
 

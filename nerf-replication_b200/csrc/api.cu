@@ -300,14 +300,16 @@ static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n
     const bool tu = c.train_u != 0;
     uint8_t* prune_mask = nullptr;       // a-M: fine-pass validity mask (fast_sampling); masked samples get raw = 0
     if (c.fast_sampling) {
-      if (keep) return h->fail(NERF_E_INVALID, "fast_sampling (ESS/ERT mask) is built for the render path only, not the fused training step");
       char nb[32]; snprintf(nb, 32, "r%d.prune", slot);
       if ((rc = h->buf(nb, (size_t)n * Nt, &prune_mask))) return rc;
     }
     // fast_sampling == 2 (bf16 tensor-core path): masked rows are not evaluated at all -- sample_pdf also emits the
-    // compacted list of valid rows, raw_f is zero-filled and the fine MLP pass walks the list (same results as the mask)
+    // compacted list of valid rows, raw_f is zero-filled and the fine MLP pass walks the list (same results as the mask).
+    // The training forward (keep) always masks: its tile images are indexed by row for the backward kernels.  A masked
+    // sample has raw = 0, hence weight 0 and relu'(0) = 0: composite_bwd hands the MLP backward an exactly zero d_raw row,
+    // which is the reference's autograd through `out[m] = flat` (network.py:238-253) -- no gradient from pruned samples.
     int32_t *row_list = nullptr, *row_count = nullptr;
-    if (c.fast_sampling == 2 && c.precision == NERF_PRECISION_BF16 && h->tc_variant != 1) {
+    if (c.fast_sampling == 2 && !keep && c.precision == NERF_PRECISION_BF16 && h->tc_variant != 1) {
       char nb[2][32]; snprintf(nb[0], 32, "r%d.rows", slot); snprintf(nb[1], 32, "r%d.nrows", slot);
       if ((rc = h->buf(nb[0], (size_t)n * Nt, &row_list)) || (rc = h->buf(nb[1], 1, &row_count))) return rc;
       NERF_CUDA_TRY(h, cudaMemsetAsync(row_count, 0, sizeof(int32_t), st));

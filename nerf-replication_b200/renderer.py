@@ -54,7 +54,7 @@ class Renderer:
         self.weights_threshold = knob(cfg, "weights_threshold", 0.25)
         self.return_dict = bool(getattr(cfg, "return_dict", False))
         # fast_sampling (ESS/ERT, volume_renderer.py:116-244,359-374): the engine builds the reference's validity mask in the
-        # sample_pdf kernel and zeroes the masked fine samples' raw output (render path; the fused training step refuses it)
+        # sample_pdf kernel; masked fine samples get raw = 0 (rendering skips them altogether, training masks them)
 
     def _engine(self):
         return self.net.engine(n_samples=self.N_samples, n_importance=self.N_importance, white_bkgd=self.white_bkgd,

@@ -137,8 +137,44 @@ def fast_cases(ref):
     fast_case(ref, "fast_thin_64rays", O.fog_state_dict(0, bias=-0.015), ro, rd, 2e-4)     # 26 empty rays, background rule
 
 
+def fast_train_case(ref, name="train_fast_fog_32rays", thr=0.02, n=32):
+    """a-M under autograd: the reference render with fast_sampling=True inside the restated loss (trainers/nerf.py:27-33);
+    pruned fine samples get raw = 0 by `out[m] = flat` (network.py:238-253) and carry no gradient."""
+    sd = O.fog_state_dict(0)
+    o, d, gt, _, _ = O.synthetic_train_batch(0, 0, n, 100, 100)
+    net_t = ref_network(ref, sd)
+    rr = ref.Renderer(net_t)
+    rr.fast_sampling, rr.weights_threshold = True, thr
+    with ref_loader.silenced():
+        rgb, _ = rr.render({"rays_o": o[None], "rays_d": d[None]})
+    loss = torch.nn.functional.mse_loss(rgb, gt)
+    loss.backward()
+    gref = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in net_t.parameters()])
+    tr = O.Trainer(sd, fast_sampling=True, weights_threshold=thr)
+    lo = tr.forward_backward(o, d, gt)
+    close(loss.detach(), lo, name + "/loss", 1e-6)
+    rel = close(gref, tr.grads_flat(), name + "/grad", 1e-5)
+    taps = {}
+    with torch.no_grad():
+        O.render(sd, o, d, taps=taps, fast_sampling=True, weights_threshold=thr)
+    plain = O.Trainer(sd)
+    lo_plain = plain.forward_backward(o, d, gt)
+    offs = np.cumsum([0] + [sd[k].numel() for k in O.state_dict_keys()])
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), loss=loss.item(), loss_unpruned=float(lo_plain), n_rays=n, weights_threshold=thr,
+                        valid_fraction=float(taps["valid_mask"].float().mean()),
+                        grad_sum=np.array([gref[offs[i]:offs[i + 1]].double().sum().item() for i in range(len(offs) - 1)]),
+                        grad_abs=np.array([gref[offs[i]:offs[i + 1]].double().abs().sum().item() for i in range(len(offs) - 1)]),
+                        grad_head=np.stack([np.pad(gref[offs[i]:offs[i + 1]][:8].numpy(), (0, max(0, 8 - (offs[i + 1] - offs[i])))) for i in range(len(offs) - 1)]))
+    print("golden %s: loss %.8f (unpruned %.8f), %.1f%% of the fine samples valid, grad rel diff oracle-vs-reference %.2e"
+          % (name, loss.item(), float(lo_plain), 100 * float(taps["valid_mask"].float().mean()), rel))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
+    if "--fast-train-only" in sys.argv:
+        torch.set_num_threads(1)
+        fast_train_case(ref_loader.load_reference())
+        return
     if "--fast-only" in sys.argv:        # adds the a-M goldens without rewriting the others
         torch.set_num_threads(1)
         fast_cases(ref_loader.load_reference())
@@ -198,6 +234,7 @@ def main():
     render_case(ref, "render_sharp_black_bkgd", sd_sharp, ro[:16], rd[:16], 64, 128, False)
     render_case(ref, "render_sharp_128_256", sd_sharp, ro[:8], rd[:8], 128, 256)
     fast_cases(ref)
+    fast_train_case(ref)
 
     # -- training: reference render under autograd + the restated loss/clip/Adam loop, 4 steps
     #    (trainer.py:53 is broken as shipped -- SURVEY fact 9 -- so the loop is the composition the

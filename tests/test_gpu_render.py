@@ -188,13 +188,47 @@ def test_render_fast_sampling_fp32_vs_reference_golden(oracle, case):
     eng.close()
 
 
-def test_fast_sampling_refused_by_fused_training(oracle):
-    eng = make_engine(oracle, oracle.init_state_dict(0), "bf16", fast_sampling=True)
-    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, 8, 100, 100)
-    grad = torch.zeros(eng._keep.numel(), device="cuda")
-    with pytest.raises(Exception, match="render path only"):
-        eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad)
-    eng.close()
+def test_fast_sampling_in_the_fused_training_step(oracle):
+    """a-M under autograd: pruned fine samples get raw = 0 and carry no gradient (network.py:238-253).  fp32 engine vs the
+    reference's own loss (golden from its render with fast_sampling=True inside the restated MSE step) and vs the oracle's
+    gradients; the bf16 tensor-core path within its training gate; work skipping (mode 2) falls back to masking here."""
+    g = load_golden("train_fast_fog_32rays")
+    thr, n = float(g["weights_threshold"]), int(g["n_rays"])
+    sd = oracle.fog_state_dict(0)
+    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, n, 100, 100)
+    tr = oracle.Trainer(sd, fast_sampling=True, weights_threshold=thr)
+    loss_ref = float(tr.forward_backward(o, d, gt))
+    g_ref = tr.grads_flat()
+    assert abs(loss_ref - float(g["loss"])) <= 1e-6 * loss_ref and abs(float(g["loss"]) - float(g["loss_unpruned"])) > 1e-6
+    losses = {}
+    for precision, mode in (("fp32", 1), ("bf16", 1), ("bf16", 2)):
+        eng = make_engine(oracle, sd if precision == "fp32" else oracle.round_weights_bf16(sd), precision, fast_sampling=mode, weights_threshold=thr)
+        grad = torch.zeros(eng._keep.numel(), device="cuda")
+        loss = float(eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad))
+        losses[(precision, mode)] = loss
+        if precision == "fp32":
+            assert abs(loss - float(g["loss"])) <= 2e-6 * loss_ref, (loss, float(g["loss"]))
+            off = 0
+            for k in oracle.state_dict_keys():
+                n_k = sd[k].numel()
+                ref_k, got_k = g_ref[off:off + n_k], grad[off:off + n_k].cpu()
+                off += n_k
+                scale = float(ref_k.abs().max())
+                if scale == 0.0:
+                    assert float(got_k.abs().max()) == 0.0, k
+                    continue
+                tol = (2e-2 if k.startswith("model.") else 1e-3) * scale        # coarse net: gradient only through the inverse CDF
+                assert maxabs(got_k, ref_k) <= tol, (k, maxabs(got_k, ref_k), scale)
+        else:
+            assert abs(loss - loss_ref) <= 1e-2 * loss_ref
+            cos = float(torch.nn.functional.cosine_similarity(grad[595844:].cpu(), g_ref[595844:], dim=0))
+            assert cos >= 0.997, cos
+        # pruning changes the step: the same call without fast_sampling gives the unpruned loss
+        eng.configure(fast_sampling=0)
+        plain = float(eng.forward_backward(o.cuda(), d.cuda(), gt.cuda(), grad))
+        assert abs(plain - float(g["loss_unpruned"])) <= (2e-6 if precision == "fp32" else 1e-2) * loss_ref
+        eng.close()
+    assert losses[("bf16", 1)] == losses[("bf16", 2)]
 
 
 @pytest.mark.parametrize("case", sorted(FAST_CASES))

@@ -127,3 +127,21 @@ def test_composite_properties(oracle):
     assert (rgb >= -1e-6).all() and (rgb <= 1 + 1e-5).all()
     rgb_b, _, _, _ = oracle.composite(raw, t, False)
     torch.testing.assert_close(rgb_b + (1 - acc)[:, None], rgb)
+
+
+def test_fast_sampling_training_golden(oracle):
+    """a-M under autograd: the restated MSE step around the oracle render with fast_sampling=True against the reference's
+    own loss and per-tensor gradient sums (oracle/make_golden.py --fast-train-only)."""
+    g = load_golden("train_fast_fog_32rays")
+    torch.set_num_threads(1)
+    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, int(g["n_rays"]), 100, 100)
+    tr = oracle.Trainer(oracle.fog_state_dict(0), fast_sampling=True, weights_threshold=float(g["weights_threshold"]))
+    loss = float(tr.forward_backward(o, d, gt))
+    assert abs(loss - float(g["loss"])) <= 1e-6 * loss
+    flat, off = tr.grads_flat(), 0
+    for i, k in enumerate(oracle.state_dict_keys()):
+        n = tr.sd[k].numel()
+        seg = flat[off:off + n]
+        off += n
+        assert abs(float(seg.double().abs().sum()) - g["grad_abs"][i]) <= 1e-4 * max(g["grad_abs"][i], 1e-12), k
+        assert np.allclose(seg[:8].numpy(), g["grad_head"][i][:min(8, n)], rtol=1e-3, atol=1e-9 + 1e-4 * float(seg.abs().max())), k
