@@ -310,6 +310,55 @@ __device__ __forceinline__ void warp_bitonic_sort(float* keys, int* kidx, int Np
   }
 }
 
+// Merge of two sorted lists already in shared memory -- coarse depths tc[0..Nc) and fine depths keys[Nc..Nc+Nf) -- into
+// keys/kidx[0..Nt) in exactly the order the stable sort above produces (coarse before fine on equal depths): every element
+// finds its output slot by one binary search in the other list (merge path), ~45 probes per lane at 64+128 instead of the
+// 36 compare-exchange rounds of the bitonic network.  Returns false (nothing written) when either list is not monotone
+// (random u in training, or an inverse-CDF rounding that steps back by an ulp) or the per-lane slots do not fit.
+constexpr int kMergeSlots = 16;   // elements per lane held in registers: Nc + Nf <= 512
+__device__ __forceinline__ bool warp_merge_sorted(const float* tc, float* keys, int* kidx, int Nc, int Nf, int lane) {
+  const float* tf = keys + Nc;
+  const int per_c = (Nc + 31) >> 5, per_f = (Nf + 31) >> 5;
+  if (per_c + per_f > kMergeSlots) return false;
+  bool ok = true;
+  for (int i = lane; i + 1 < Nc; i += 32) ok = ok && tc[i] <= tc[i + 1];
+  for (int k = lane; k + 1 < Nf; k += 32) ok = ok && tf[k] <= tf[k + 1];
+  if (!__all_sync(0xffffffffu, ok)) return false;
+  float val[kMergeSlots];
+  int pos[kMergeSlots];
+#pragma unroll
+  for (int j = 0; j < kMergeSlots; ++j) {
+    pos[j] = -1;
+    if (j < per_c) {
+      const int i = lane + 32 * j;
+      if (i < Nc) {
+        const float v = tc[i];
+        int lo = 0, hi = Nf;                  // number of fine depths strictly below v
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (tf[mid] < v) lo = mid + 1; else hi = mid; }
+        val[j] = v; pos[j] = i + lo;
+      }
+    } else if (j < per_c + per_f) {
+      const int k = lane + 32 * (j - per_c);
+      if (k < Nf) {
+        const float v = tf[k];
+        int lo = 0, hi = Nc;                  // number of coarse depths at or below v
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (tc[mid] <= v) lo = mid + 1; else hi = mid; }
+        val[j] = v; pos[j] = k + lo;
+      }
+    }
+  }
+  __syncwarp();                               // every probe of keys[Nc..] is done before the slots are overwritten
+#pragma unroll
+  for (int j = 0; j < kMergeSlots; ++j) {
+    if (pos[j] >= 0) {
+      keys[pos[j]] = val[j];
+      kidx[pos[j]] = j < per_c ? lane + 32 * j : Nc + lane + 32 * (j - per_c);
+    }
+  }
+  __syncwarp();
+  return true;
+}
+
 __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float* __restrict__ t_c, int64_t n, int Nc,
                                   int Nf, int Npad, const float* __restrict__ u, int philox, uint64_t seed,
                                   uint64_t call_id, const float* __restrict__ cdf_in, float* __restrict__ t_fine,
@@ -347,7 +396,7 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
     for (int k = Nt + lane; k < Npad; k += 32) { s.keys[k] = __int_as_float(0x7f800000); s.kidx[k] = 0x7fffffff; }
     __syncwarp();
     if (t_sorted || sort_idx || (prune.on && (prune.mask_sorted || prune.row_list))) {
-      warp_bitonic_sort(s.keys, s.kidx, Npad, lane);
+      if (!warp_merge_sorted(s.tc, s.keys, s.kidx, Nc, Nf, lane)) warp_bitonic_sort(s.keys, s.kidx, Npad, lane);
       for (int k = lane; k < Nt; k += 32) {
         if (t_sorted) t_sorted[ray * Nt + k] = s.keys[k];
         if (sort_idx) sort_idx[ray * Nt + k] = s.kidx[k];
