@@ -45,31 +45,44 @@ __host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li
 size_t tc_wpack_bytes() { return (size_t)2 * kNumStages * kStageBytes; }
 
 // Packs fp32 [out][in] weights into the stage images the kernel streams: stage = [N rows x 64 k] bf16,
-// K-major, 128B swizzle.  One thread per (net, stage, n, k).
+// K-major, 128B swizzle.  One thread per 16-byte chunk (net, stage, n, 8 consecutive k): the schedule lookup is done once
+// per chunk, the eight source weights are consecutive floats, the destination is one 16-byte store.
 __global__ void pack_weights_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack) {
-  const int64_t total = (int64_t)2 * kNumStages * 256 * 64;
+  const int64_t total = (int64_t)2 * kNumStages * 256 * 8;
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    const int k = (int)(e & 63), n = (int)((e >> 6) & 255);
-    const int s = (int)((e >> 14) % kNumStages), net = (int)((e >> 14) / kNumStages);
+    const int kc = (int)(e & 7), n = (int)((e >> 3) & 255);
+    const int s = (int)((e >> 11) % kNumStages), net = (int)((e >> 11) / kNumStages);
     int li = 0;
     while (li + 1 < kNumSched && sched_start(li + 1) <= s) ++li;
     const int kb = s - sched_start(li);
     if (n >= sched_n(li)) continue;
     const int layer = sched_layer(li);
     const LayerDim d = layer_dim(layer);
-    int col;   // input column of the reference weight, -1 = zero padding
-    if (li == 0) col = k < 63 ? k : -1;
-    else if (li == 5) col = kb == 0 ? (k < 63 ? k : -1) : 63 + (kb - 1) * 64 + k;     // [pts63 | h256]
-    else if (li == 9) col = kb < 4 ? kb * 64 + k : (k < 27 ? 256 + k : -1);           // [feature256 | dir27]
-    else col = kb * 64 + k;
-    const float w = col < 0 ? 0.f : flat[(int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + (int64_t)n * d.in + col];
-    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + s) * kStageBytes + sw128_offset(n, k >> 3) + (k & 7) * 2;
-    *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16(w);
+    const float* wrow = flat + (int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + (int64_t)n * d.in;
+    uint32_t pk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float w2[2];
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const int k = kc * 8 + 2 * j + h2;
+        int col;   // input column of the reference weight, -1 = zero padding
+        if (li == 0) col = k < 63 ? k : -1;
+        else if (li == 5) col = kb == 0 ? (k < 63 ? k : -1) : 63 + (kb - 1) * 64 + k;     // [pts63 | h256]
+        else if (li == 9) col = kb < 4 ? kb * 64 + k : (k < 27 ? 256 + k : -1);           // [feature256 | dir27]
+        else col = kb * 64 + k;
+        w2[h2] = col < 0 ? 0.f : __ldg(wrow + col);
+      }
+      const __nv_bfloat162 b2 = __floats2bfloat162_rn(w2[0], w2[1]);
+      pk[j] = *reinterpret_cast<const uint32_t*>(&b2);
+    }
+    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + s) * kStageBytes + sw128_offset(n, kc);
+    *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   }
 }
 
 void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st) {
-  pack_weights_kernel<<<h->num_sms * 8, 256, 0, st>>>(flat, wpack);
+  pack_weights_kernel<<<h->num_sms * 4, 256, 0, st>>>(flat, wpack);
   h->launches++;
 }
 

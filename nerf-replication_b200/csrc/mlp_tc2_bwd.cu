@@ -80,26 +80,38 @@ size_t tc_bwd_wpack_bytes() { return (size_t)2 * bw::kNumStages * bw::kStageImag
 // for n < ncols (zero beyond), [N rows x 64 k] bf16, K-major, 128B swizzle.
 __global__ void pack_dgrad_weights_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack) {
   using namespace bw;
-  const int64_t total = (int64_t)2 * kNumStages * 256 * 64;
+  const int64_t total = (int64_t)2 * kNumStages * 256 * 8;     // one thread per 16-byte chunk: (net, stage, n, 8 consecutive k)
   for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    const int k = (int)(e & 63), n = (int)((e >> 6) & 255);
-    const int stg = (int)((e >> 14) % kNumStages), net = (int)((e >> 14) / kNumStages);
+    // n fastest: neighbouring threads read neighbouring columns of the same weight rows
+    const int n = (int)(e & 255), kc = (int)((e >> 8) & 7);
+    const int stg = (int)((e >> 11) % kNumStages), net = (int)((e >> 11) / kNumStages);
     int s = 0;
     while (s + 1 < kNumSteps && step_stage0(s + 1) <= stg) ++s;
     const int kb = stg - step_stage0(s);
     if (n >= step_n(s)) continue;
     const int layer = step_layer(s);
     const LayerDim d = layer_dim(layer);
-    const int out = kb * 64 + k;                     // output feature of the layer = reduction index of dgrad
-    float w = 0.f;
-    if (n < step_ncols(s) && out < d.out) w = flat[(int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + (int64_t)out * d.in + step_col0(s) + n];
-    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + stg) * kStageImage + sw128_offset(n, k >> 3) + (k & 7) * 2;
-    *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16(w);
+    const bool col_ok = n < step_ncols(s);
+    const float* wcol = flat + (int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + step_col0(s) + n;
+    uint32_t pk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float w2[2];
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const int out = kb * 64 + kc * 8 + 2 * j + h2;     // output feature of the layer = reduction index of dgrad
+        w2[h2] = (col_ok && out < d.out) ? __ldg(wcol + (int64_t)out * d.in) : 0.f;
+      }
+      const __nv_bfloat162 b2 = __floats2bfloat162_rn(w2[0], w2[1]);
+      pk[j] = *reinterpret_cast<const uint32_t*>(&b2);
+    }
+    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + stg) * kStageImage + sw128_offset(n, kc);
+    *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   }
 }
 
 void tc_pack_dgrad_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st) {
-  pack_dgrad_weights_kernel<<<h->num_sms * 8, 256, 0, st>>>(flat, wpack);
+  pack_dgrad_weights_kernel<<<h->num_sms * 4, 256, 0, st>>>(flat, wpack);
   h->launches++;
 }
 
