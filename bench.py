@@ -238,7 +238,7 @@ def main():
     if world > 1:
         dist.barrier()
 
-    from oracle import nerf_oracle as O        # inputs (camera poses) only come from the shared synthetic spec
+    from nerf_replication_b200 import synthetic as SYN     # lego-shaped cameras / batches; rays from the engine's get_rays kernel
     from nerf_replication_b200 import config as C
     from nerf_replication_b200.network import Network
     from nerf_replication_b200.renderer import Renderer
@@ -259,7 +259,6 @@ def main():
     renderer = Renderer(net, cfg=cfg)
     eng = renderer._engine()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    focal = O.focal_from_fov(W)
 
     def barrier():
         if world > 1:
@@ -271,11 +270,11 @@ def main():
         r0, r1 = shard_range(H, rank, world)          # this rank's row band of every view
         rays_o, rays_d = [], []
         for v in range(world):
-            o, d = O.get_rays_np(O.lego_pose(v, max(world, 8)), H, W, pixel_ids=None)
-            rays_o.append(torch.from_numpy(o[r0 * W:r1 * W]))
-            rays_d.append(torch.from_numpy(d[r0 * W:r1 * W]))
-        host_o = torch.cat(rays_o).pin_memory()
-        host_d = torch.cat(rays_d).pin_memory()
+            o, d = SYN.view_rays(eng, v, max(world, 8), H, W, r0, r1)
+            rays_o.append(o)
+            rays_d.append(d)
+        host_o = torch.cat(rays_o).cpu().pin_memory()
+        host_d = torch.cat(rays_d).cpu().pin_memory()
         dev_o, dev_d = host_o.cuda(), host_d.cuda()
         n_local = dev_o.shape[0]
         host_rgb = torch.empty(n_local, 3).pin_memory()
@@ -296,8 +295,8 @@ def main():
         trainer = FusedTrainer(net, cfg=cfg)
         batches = []
         for s in range(8):
-            o, d, gt, _, _ = O.synthetic_train_batch(s, rank, TRAIN_RAYS)
-            batches.append((o.pin_memory(), d.pin_memory(), gt.pin_memory()))
+            o, d, gt = SYN.train_batch(eng, s, rank, TRAIN_RAYS, H, W)
+            batches.append((o.cpu().pin_memory(), d.cpu().pin_memory(), gt.cpu().pin_memory()))
         dev_batches = [tuple(t.cuda() for t in b) for b in batches]
         loss_host = torch.empty((), pin_memory=True)
 
@@ -363,8 +362,8 @@ def main():
         from nerf_replication_b200.trainer import Recorder, Trainer, make_data_loader
         n_views = 8
         imgs = np.random.RandomState(rank).randint(0, 256, size=(n_views, H, W, 3), dtype=np.uint8)
-        poses = np.stack([O.lego_pose(v, n_views) for v in range(n_views)])
-        ds = Dataset(net=net, images=imgs, transform_matrices=poses, camera_angle_x=O.CAMERA_ANGLE_X, split="train", seed=rank,
+        poses = np.stack([SYN.lego_pose(v, n_views) for v in range(n_views)])
+        ds = Dataset(net=net, images=imgs, transform_matrices=poses, camera_angle_x=SYN.CAMERA_ANGLE_X, split="train", seed=rank,
                      n_rays=TRAIN_RAYS)
         opt = FusedAdam(net, lr=5e-4, eps=1e-8, clip=40.0)
         opt.m, opt.v, opt.step_count = trainer.m, trainer.v, trainer.step_count      # continue the same optimisation state

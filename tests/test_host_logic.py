@@ -109,3 +109,13 @@ def test_gradient_allreduce_world2_gloo():
         torch.testing.assert_close(head, base * 1.5)     # mean of g and 2g
         assert last == 1191687 * 1.5
         assert out[world + r] == 800                      # row bands cover the image exactly once
+
+
+def test_synthetic_workload_spec_matches_the_oracle():
+    """bench.py builds its cameras from the package's synthetic spec; the parity tests use the oracle's: same numbers."""
+    import numpy as np
+    from nerf_replication_b200 import synthetic as SYN
+    from oracle import nerf_oracle as O
+    assert SYN.CAMERA_ANGLE_X == O.CAMERA_ANGLE_X and SYN.focal_from_fov(800) == O.focal_from_fov(800)
+    for k, nv in ((0, 8), (5, 8), (3, 100)):
+        assert np.array_equal(SYN.lego_pose(k, nv), O.lego_pose(k, nv))
