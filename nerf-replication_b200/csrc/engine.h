@@ -132,6 +132,7 @@ int mlp_fp32_backward(NerfEngine* h, int net, const RowSrc& src, const float* d_
 
 // ---- mlp_tc.cu (tcgen05) ------------------------------------------------------------------------
 size_t tc_wpack_bytes();
+size_t tc_wpack_bias_offset();   // byte offset of the bias slabs ([net][schedule entry] x 8 KB) inside the packed buffer
 void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
 int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
 

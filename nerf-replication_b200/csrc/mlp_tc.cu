@@ -42,7 +42,10 @@ __host__ __device__ constexpr int sched_n(int li) { return li == 9 ? 128 : 256; 
 // schedule index -> reference layer id (state_dict order): 0..7 trunk, 8 -> feature(9), 9 -> views(8)
 __host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li == 8 ? L_FEAT : L_VIEWS); }
 
-size_t tc_wpack_bytes() { return (size_t)2 * kNumStages * kStageBytes; }
+// after the stage images of both nets: per (net, schedule entry) one 8 KB bias slab (csrc/mlp_tc2.cu folds the bias into the GEMM)
+constexpr size_t kBiasSlabBytes = 8192;
+size_t tc_wpack_bias_offset() { return (size_t)2 * kNumStages * kStageBytes; }
+size_t tc_wpack_bytes() { return tc_wpack_bias_offset() + (size_t)2 * kNumSched * kBiasSlabBytes; }
 
 // Packs fp32 [out][in] weights into the stage images the kernel streams: stage = [N rows x 64 k] bf16,
 // K-major, 128B swizzle.  One thread per 16-byte chunk (net, stage, n, 8 consecutive k): the schedule lookup is done once
@@ -81,9 +84,33 @@ __global__ void pack_weights_kernel(const float* __restrict__ flat, __nv_bfloat1
   }
 }
 
+// Bias slabs for the CTA-pair kernel: the bias enters the accumulator through one extra K = 16 MMA per layer, A = a constant
+// slab whose columns 0..2 are 1.0, B = this slab: row n holds (hi, mid, lo, 0 ...) with hi + mid + lo = bias[n] split into three
+// bf16 terms (24 mantissa bits, products by 1.0 are exact, fp32 accumulation).  Layout: un-swizzled K-major core matrices
+// (8 rows x 16 bytes), element (r, k) of a CTA's half at (r / 8) * 256 + (k / 8) * 128 + (r % 8) * 16 + (k % 8) * 2; each CTA
+// of the pair owns N / 2 consecutive rows, its half starts at rank * 4096.  One thread per row.
+__global__ void pack_bias_slabs_kernel(const float* __restrict__ flat, uint8_t* __restrict__ slabs) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= 2 * kNumSched * 256) return;
+  const int n = e & 255, li = (e >> 8) % kNumSched, net = (e >> 8) / kNumSched;
+  const int N = sched_n(li);
+  if (n >= N) return;
+  const float b = __ldg(flat + (int64_t)net * NERF_PARAMS_PER_NET + b_off(sched_layer(li)) + n);
+  const __nv_bfloat16 hi = __float2bfloat16_rn(b);
+  const float r1 = b - __bfloat162float(hi);
+  const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+  const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+  const int rank = n / (N / 2), r = n % (N / 2);
+  uint8_t* dst = slabs + ((size_t)net * kNumSched + li) * kBiasSlabBytes + (size_t)rank * 4096 + (r >> 3) * 256 + (r & 7) * 16;
+  const uint32_t w0 = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(mid) << 16);
+  *reinterpret_cast<uint4*>(dst) = make_uint4(w0, (uint32_t)__bfloat16_as_ushort(lo), 0u, 0u);
+  *reinterpret_cast<uint4*>(dst + 128) = make_uint4(0u, 0u, 0u, 0u);
+}
+
 void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st) {
   pack_weights_kernel<<<h->num_sms * 4, 256, 0, st>>>(flat, wpack);
-  h->launches++;
+  pack_bias_slabs_kernel<<<(2 * kNumSched * 256 + 255) / 256, 256, 0, st>>>(flat, reinterpret_cast<uint8_t*>(wpack) + tc_wpack_bias_offset());
+  h->launches += 2;
 }
 
 // ---- the fused forward kernel ---------------------------------------------------------------------

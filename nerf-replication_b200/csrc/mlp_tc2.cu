@@ -18,7 +18,10 @@
 //   warps 2-5   tile X: positional encoding -> bf16 A operand; per layer TMEM -> +bias (shared memory), ReLU ->
 //               bf16 -> A operand of the next layer (in place); sigma / rgb heads on CUDA cores
 //   warps 6-9   same for tile Y
-// Shared memory (bytes): A_X 64K | A_Y 64K | PE_X 16K | PE_Y 16K | W ring 3 x 16K | biases 9.5K | heads 2.5K | barriers
+// Shared memory (bytes): A_X 64K | A_Y 64K | PE_X 16K | PE_Y 16K | W ring 3 x 16K | ones slab 4K | bias ring 2 x 4K | heads 2.5K | barriers
+// Biases: folded into the GEMM -- every layer starts with one K = 16 MMA (A = constant slab whose columns 0..2 are 1.0,
+// B = the layer's bias slab: bias split into three bf16 terms) that also initialises the accumulator, so the epilogue is
+// TMEM -> ReLU/bf16 -> st.shared only (the 64 LDS.128 + 64 FADD2 per row and layer it replaces cost 11 % of the kernel).
 #include "engine.h"
 #include "tc_common.cuh"
 #include "rows.cuh"
@@ -38,12 +41,15 @@ constexpr int kRing = 3;
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
 constexpr int kNumStages = 39;
 constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
-constexpr int kBiasFloats = kNumSched * 256;    // bias of schedule entry li at [li*256, +N)
+constexpr int kOnesBytes = 4096;                // constant A slab of the bias MMA: 128 rows x 16 k, columns 0..2 = 1.0
+constexpr int kBiasSlabBytes = 8192;            // packed bias slab of one schedule entry (both halves), mlp_tc.cu pack_bias_slabs_kernel
 constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
 constexpr uint32_t kOffBias = kOffW + kRing * kHalfBytes;         // 212992
-constexpr uint32_t kOffHeads = kOffBias + kBiasFloats * 4;        // 223232: w_alpha[256] | w_rgb[384]
-constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;         // 225792
-constexpr uint32_t kSmemBytes = kOffBar + 256;                    // 226048 <= 232448
+constexpr int kBiasRing = 2;                                      // bias slabs have their own small ring (4 KB slots)
+constexpr uint32_t kOffBiasRing = kOffBias + kOnesBytes;          // 217088
+constexpr uint32_t kOffHeads = kOffBiasRing + kBiasRing * 4096;   // 225280: w_alpha[256] | w_rgb[384]
+constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;         // 227840
+constexpr uint32_t kSmemBytes = kOffBar + 256;                    // 228096 <= 232448
 
 __host__ __device__ constexpr int sched_nkb(int li) { return li == 0 ? 1 : (li == 5 || li == 9) ? 5 : 4; }
 __host__ __device__ constexpr int sched_start(int li) {
@@ -56,7 +62,7 @@ __host__ __device__ constexpr int sched_n(int li) { return li == 9 ? 128 : 256; 
 __host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li == 8 ? L_FEAT : L_VIEWS); }
 
 struct Bars {
-  uint64_t w_full[kRing], w_empty[kRing], acc_full[2], act_ready[2];
+  uint64_t w_full[kRing], w_empty[kRing], b_full[kBiasRing], b_empty[kBiasRing], acc_full[2], act_ready[2];
   uint32_t tmem_slot;
 };
 
@@ -126,17 +132,14 @@ __device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, 
 // grow != nullptr (training forward): the chunk is also stored to this row of the layer's arena blocks, and mbits
 // receives the ReLU bit mask of the 32 columns.
 template <int MODE>
-__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const float* __restrict__ s_bias,
+__device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
                                           const float* __restrict__ s_walpha, float& sigma, uint8_t* sAct,
                                           uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint8_t* gmask) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);     // warp-uniform address: broadcast
-    float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
-    float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
-    add2(f0, f1, bb.x, bb.y);
-    add2(f2, f3, bb.z, bb.w);
+    const float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);      // bias already in the accumulator
+    const float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
     if (MODE == 2) {
       pk[2 * j] = pack_bf16x2(f0, f1); pk[2 * j + 1] = pack_bf16x2(f2, f3);
     } else {
@@ -163,7 +166,7 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0, const
 // Whole 256-column epilogue of one tile row, TMEM loads software-pipelined against the math of the previous chunk.
 // grow / gmask (training forward): this row of the layer's arena blocks / of its bit-mask record.
 template <int MODE>
-__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_walpha,
+__device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_walpha,
                                           float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor, uint8_t* grow,
                                           uint8_t* gmask) {
   uint32_t va[32], vb[32];
@@ -172,27 +175,24 @@ __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restric
   for (int c = 0; c < 8; c += 2) {
     tmem_wait_ld();
     tmem_ld32(taddr + (c + 1) * 32, vb);
-    epi_chunk<MODE>(va, c * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
+    epi_chunk<MODE>(va, c * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
     tmem_wait_ld();
     if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
-    epi_chunk<MODE>(vb, (c + 1) * 32, s_bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
+    epi_chunk<MODE>(vb, (c + 1) * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
   }
 }
 
 // View-branch epilogue: 128 columns, ReLU, then the 128 -> 3 rgb head on CUDA cores.
 template <bool SAVE>
-__device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_bias, const float* __restrict__ s_wrgb,
+__device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_wrgb,
                                           float& r0, float& r1, float& r2, uint8_t* grow, uint8_t* gmask) {
   uint32_t va[32], vb[32];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);
-      float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
-      float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
-      add2(f0, f1, bb.x, bb.y);
-      add2(f2, f3, bb.z, bb.w);
+      const float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
+      const float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
       if (SAVE) { pk[2 * j] = pack_bf16x2_relu(f0, f1); pk[2 * j + 1] = pack_bf16x2_relu(f2, f3); }
       const float hv[4] = {fmaxf(f0, 0.f), fmaxf(f1, 0.f), fmaxf(f2, 0.f), fmaxf(f3, 0.f)};
       const float4 w0 = *reinterpret_cast<const float4*>(s_wrgb + c0 + 4 * j);
@@ -228,14 +228,15 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
-                       const float* __restrict__ P, int64_t M, int64_t n_pair, uint8_t* __restrict__ act_arena) {
+                       const uint8_t* __restrict__ wbias, const float* __restrict__ P, int64_t M, int64_t n_pair,
+                       uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if (!SAVE && src.row_count) {      // compacted row list (fast_sampling work skipping): the row count lives on the device
     M = min((int64_t)__ldg(src.row_count), M);
     n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
   }
+  constexpr int kReps = SAVE ? 2 : 1;            // weight passes per layer (training: once per tile, see the issuer)
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
-  float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
   float* s_wrgb = s_walpha + 256;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -245,11 +246,14 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA12, smem_u32(smem));   // swizzle-128B needs 1024B alignment
   if (tid == 0) {
     for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
+    for (int i = 0; i < kBiasRing; ++i) { mbar_init(&sb.b_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.b_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
     fence_barrier_init();
   }
-  for (int li = 0; li < kNumSched; ++li)
-    for (int i = tid; i < sched_n(li); i += kThreads) s_bias[li * 256 + i] = __ldg(P + b_off(sched_layer(li)) + i);
+  // constant A slab of the bias MMAs: 128 rows x 16 k bf16, un-swizzled K-major core matrices, columns 0..2 = 1.0
+  for (int i = tid; i < kOnesBytes / 16; i += kThreads)
+    reinterpret_cast<uint4*>(smem + kOffBias)[i] = (i & 8) ? make_uint4(0u, 0u, 0u, 0u) : make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);
+  fence_proxy_async_smem();
   for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(P + w_off(L_ALPHA) + i);
   for (int i = tid; i < 384; i += kThreads) s_wrgb[i] = __ldg(P + w_off(L_RGB) + i);
   cluster_sync_all();                      // barrier inits visible cluster-wide before any remote arrive / multicast commit
@@ -262,19 +266,26 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
   if (warp == 0) {
     // ===== weight producer (both CTAs): my half of every stage =====
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t it = 0, itb = 0;
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li) {
           const uint32_t bytes = (uint32_t)sched_n(li) * 64u;                 // half of the stage: N/2 rows x 128 B
-          for (int rep = 0; rep < (SAVE ? 2 : 1); ++rep)                      // training: once per tile (see the issuer)
+          for (int rep = 0; rep < kReps; ++rep) {                             // training: once per tile (see the issuer)
+            {                                                                 // the layer's bias slab (N/2 rows x 32 B), own ring
+              const uint32_t slot = itb % kBiasRing, par = (itb / kBiasRing) & 1u;
+              ++itb;
+              mbar_wait(&sb.b_empty[slot], par ^ 1u, 0x18 + slot);
+              mbar_arrive_expect_tx(&sb.b_full[slot], bytes / 4);
+              bulk_g2s(smem + kOffBiasRing + slot * 4096, wbias + (size_t)li * kBiasSlabBytes + (size_t)rank * 4096, bytes / 4, &sb.b_full[slot]);
+            }
             for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
               mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
+              const uint8_t* gsrc = reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes;
               mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
-              bulk_g2s(smem + kOffW + slot * kHalfBytes,
-                       reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes,
-                       bytes, &sb.w_full[slot]);
+              bulk_g2s(smem + kOffW + slot * kHalfBytes, gsrc, bytes, &sb.w_full[slot]);
             }
+          }
         }
       }
     }
@@ -282,19 +293,26 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
   } else if (warp == 1 && rank == 1) {
     // ===== forwarder (peer CTA): relay local weight arrival to the leader's w_full =====
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t it = 0, itb = 0;
       for (int64_t st = pair0; st < n_pair; st += pair_stride)
-        for (int s = 0; s < (SAVE ? 2 : 1) * kNumStages; ++s, ++it) {
-          const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-          mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
-          mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
-        }
+        for (int li = 0; li < kNumSched; ++li)
+          for (int rep = 0; rep < kReps; ++rep) {
+            const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
+            ++itb;
+            mbar_wait(&sb.b_full[bslot], bpar, 0x58 + bslot);
+            mbar_arrive_remote(mapa_u32(smem_u32(&sb.b_full[bslot]), 0));
+            for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
+              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+              mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
+              mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+            }
+          }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA) =====
     if (lane == 0) {
-      uint32_t it = 0, lc = 0;
+      uint32_t it = 0, itb = 0, lc = 0;
       const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE), sW = smem_u32(smem + kOffW);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li, ++lc) {
@@ -302,6 +320,11 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           const uint32_t idesc = make_idesc_bf16(256, sched_n(li));
           // A source of k-block kb: -1 = PE buffer, else hidden-activation block
           auto a_block = [&](int kb) { return li == 0 ? -1 : li == 5 ? kb - 1 : li == 9 ? (kb < 4 ? kb : -1) : kb; };
+          // bias slab: one K = 16 MMA (un-swizzled K-major operands) that also initialises the accumulator
+          auto issue_bias = [&](int tile, uint32_t bslot) {
+            umma_ss2(tmem + tile * 256u, make_smem_desc(smem_u32(smem + kOffBias), 128, 256, kLayoutNone),
+                     make_smem_desc(smem_u32(smem + kOffBiasRing) + bslot * 4096u, 128, 256, kLayoutNone), idesc, 0u);
+          };
           auto issue = [&](int tile, int kb, uint32_t slot) {
             const int ablk = a_block(kb);
             const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
@@ -309,7 +332,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
-                       make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+                       make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, 1u);
             }
           };
           if (SAVE) {
@@ -319,6 +342,14 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
             for (int tile = 0; tile < 2; ++tile) {
               mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
               tc_fence_after();
+              {
+                const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
+                ++itb;
+                mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
+                tc_fence_after();
+                issue_bias(tile, bslot);
+                umma_commit2(&sb.b_empty[bslot], 0x3);
+              }
               for (int kb = 0; kb < nkb; ++kb, ++it) {
                 const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
                 mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
@@ -331,13 +362,25 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           } else {
             // Render: every weight stage feeds both tiles before it is released (half the weight traffic; with the
             // 3-slot ring the per-tile order above starves the tensor pipe: 1075 vs 1128 TFLOP/s measured).
-            for (int kb = 0; kb < nkb; ++kb, ++it) {
-              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-              mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+            {
+              const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
+              ++itb;
+              mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
               tc_fence_after();
 #pragma unroll
               for (int tile = 0; tile < 2; ++tile) {
-                if (kb == 0) { mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile); tc_fence_after(); }
+                mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
+                tc_fence_after();
+                issue_bias(tile, bslot);
+              }
+              umma_commit2(&sb.b_empty[bslot], 0x3);
+            }
+            for (int kb = 0; kb < nkb; ++kb, ++it) {
+              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
+              mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+                tc_fence_after();
+#pragma unroll
+              for (int tile = 0; tile < 2; ++tile) {
                 issue(tile, kb, slot);
                 if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
               }
@@ -383,18 +426,17 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       for (int li = 0; li < kNumSched; ++li, ++lc) {
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
-        const float* bias = s_bias + li * 256;
         if (li < 9) {
           uint8_t* grow = gblk(li < 8 ? arena::kActH + 4 * li : arena::kActFeat);
-          if (li == 7) epi_layer<1>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
-          else if (li == 8) epi_layer<2>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr);
-          else epi_layer<0>(taddr, bias, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
+          if (li == 7) epi_layer<1>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
+          else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr);
+          else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
           if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd, gblk(arena::kActPEDir));
           signal_ready();
         } else {
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-          epi_views<SAVE>(taddr, bias, s_wrgb, r0, r1, r2, gblk(arena::kActHV), gmsk(arena::kMaskHV));
+          epi_views<SAVE>(taddr, s_wrgb, r0, r1, r2, gblk(arena::kActHV), gmsk(arena::kMaskHV));
           tc_fence_before();
           if (valid) {
             float4 o = make_float4(r0 + __ldg(P + b_off(L_RGB)), r1 + __ldg(P + b_off(L_RGB) + 1), r2 + __ldg(P + b_off(L_RGB) + 2),
@@ -430,8 +472,9 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, act_arena);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, P, M, n_pair, nullptr);
+  const uint8_t* wb = reinterpret_cast<const uint8_t*>(h->wpack) + tc_wpack_bias_offset() + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumSched * kBiasSlabBytes;
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, wb, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, wb, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));
