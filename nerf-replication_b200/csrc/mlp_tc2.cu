@@ -97,19 +97,19 @@ __device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, fl
 constexpr float kInv2PiHi = 0.15915493667125702f;          // fl(1/(2 pi))
 constexpr float kInv2PiLo = 6.4206382432985265e-09f;          // 1/(2 pi) - kInv2PiHi
 
-// Writes one 64-column bf16 K-block row: [v0 v1 v2 | sin(2^k v) cos(2^k v)]_{k<L} | zero pad, 8 columns per 16-byte chunk.
-// grow != nullptr (training forward): the same chunks also go to this row of the block's arena image (tc_arena.cuh).
+// One 64-column bf16 K-block row, [v0 v1 v2 | sin(2^k v) cos(2^k v)]_{k<L} | zero pad | 1.0, packed into 32 registers (8 chunks
+// of 8 columns).  The encoding is computed ahead of time, while the tile's MMAs run and its epilogue warps would only spin
+// on the accumulator barrier (60 + 24 MUFU pairs per row are ~4 % of the kernel when they sit between two layers).
 template <int L>
-__device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, uint32_t row_xor, const float v[3], uint8_t* grow) {
+__device__ __forceinline__ void compute_pe_block(const float v[3], uint32_t (&out)[32]) {
   float col[8];
   int n = 0, chunk = 0;
   auto push = [&](float x) {
     col[n++] = x;
     if (n == 8) {
-      const uint32_t w0 = pack_bf16x2(col[0], col[1]), w1 = pack_bf16x2(col[2], col[3]);
-      const uint32_t w2 = pack_bf16x2(col[4], col[5]), w3 = pack_bf16x2(col[6], col[7]);
-      if (grow) st_global_cs(grow + chunk * 1024, w0, w1, w2, w3);
-      store_chunk(blk, row_base, row_xor, chunk++, w0, w1, w2, w3);
+      out[4 * chunk + 0] = pack_bf16x2(col[0], col[1]); out[4 * chunk + 1] = pack_bf16x2(col[2], col[3]);
+      out[4 * chunk + 2] = pack_bf16x2(col[4], col[5]); out[4 * chunk + 3] = pack_bf16x2(col[6], col[7]);
+      ++chunk;
       n = 0;
     }
   };
@@ -125,6 +125,15 @@ __device__ __forceinline__ void write_pe_block(uint8_t* blk, uint32_t row_base, 
 #pragma unroll
   for (int z = 3 + 6 * L; z < 63; ++z) push(0.f);
   push(1.0f);     // column 63 = 1: its weight column is zero in the forward; in wgrad it yields the bias gradient
+}
+// Stores the packed row into the swizzled K-block; grow != nullptr (training forward): the same chunks also go to this row of
+// the block's arena image (tc_arena.cuh).
+__device__ __forceinline__ void store_pe_block(uint8_t* blk, uint32_t row_base, uint32_t row_xor, const uint32_t (&pe)[32], uint8_t* grow) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    if (grow) st_global_cs(grow + c * 1024, pe[4 * c], pe[4 * c + 1], pe[4 * c + 2], pe[4 * c + 3]);
+    store_chunk(blk, row_base, row_xor, c, pe[4 * c], pe[4 * c + 1], pe[4 * c + 2], pe[4 * c + 3]);
+  }
 }
 
 // One 32-column chunk of a trunk-layer epilogue: acc + bias -> (ReLU) -> bf16 -> 4 x 16-byte chunks of the next
@@ -407,23 +416,45 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
     uint32_t lc = 0;
+    // this row of pair super-tile st_: validity, global row (through the compacted row list when rows are skipped), point, view direction
+    auto row_setup = [&](int64_t st_, bool& valid_, int64_t& g_, float (&p_)[3], float (&vd_)[3]) {
+      const int64_t gl = st_ * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
+      valid_ = gl < M;
+      g_ = (!SAVE && src.row_list && valid_) ? (int64_t)__ldg(src.row_list + gl) : gl;
+      p_[0] = p_[1] = p_[2] = 0.f; vd_[0] = vd_[1] = vd_[2] = 0.f;
+      if (valid_) row_point(src, g_, p_, vd_);
+    };
+    uint32_t pe[32];                      // the next PE block of this row, packed (PE(pts) of the next super-tile or PE(dir) of this one)
+    bool valid = false;
+    int64_t g = 0;
+    float vd[3] = {0.f, 0.f, 0.f};
+    if (pair0 < n_pair) {
+      float p[3];
+      row_setup(pair0, valid, g, p, vd);
+      compute_pe_block<10>(p, pe);
+    }
     for (int64_t st = pair0; st < n_pair; st += pair_stride) {
-      const int64_t gl = st * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
-      const bool valid = gl < M;
-      const int64_t g = (!SAVE && src.row_list && valid) ? (int64_t)__ldg(src.row_list + gl) : gl;
       // training forward: this row's slice of the tile's arena blocks / bit-mask records (tc_arena.cuh)
       uint8_t* tile_base = SAVE ? act_arena + (size_t)((st * 2 + rank) * 2 + tile) * arena::act_tile_bytes() : nullptr;
       uint8_t* grow0 = SAVE ? tile_base + arena::cm_row_offset(row) : nullptr;
       uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 4 : nullptr;
       auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
       auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
-      float p[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
-      if (valid) row_point(src, g, p, vd);
-      write_pe_block<10>(sPe, row_base, row_xor, p, gblk(arena::kActPE));
+      store_pe_block(sPe, row_base, row_xor, pe, gblk(arena::kActPE));
       signal_ready();
 
       float sigma = 0.f;
+      bool nvalid = false;
+      int64_t ng = 0;
+      float nvd[3] = {0.f, 0.f, 0.f};
       for (int li = 0; li < kNumSched; ++li, ++lc) {
+        // encodings computed under this tile's MMAs: PE(dir) before layer 5's epilogue, the next super-tile's PE(pts) before the last
+        if (li == 5) compute_pe_block<4>(vd, pe);
+        if (li == 9 && st + pair_stride < n_pair) {
+          float np[3];
+          row_setup(st + pair_stride, nvalid, ng, np, nvd);
+          compute_pe_block<10>(np, pe);
+        }
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
         if (li < 9) {
@@ -432,7 +463,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr);
           else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
-          if (li == 5) write_pe_block<4>(sPe, row_base, row_xor, vd, gblk(arena::kActPEDir));
+          if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, gblk(arena::kActPEDir));
           signal_ready();
         } else {
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
@@ -446,6 +477,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
           }
         }
       }
+      valid = nvalid; g = ng; vd[0] = nvd[0]; vd[1] = nvd[1]; vd[2] = nvd[2];
     }
   }
   tc_fence_before();
