@@ -22,6 +22,7 @@
 // Biases: folded into the GEMM -- every layer starts with one K = 16 MMA (A = constant slab whose columns 0..2 are 1.0,
 // B = the layer's bias slab: bias split into three bf16 terms) that also initialises the accumulator, so the epilogue is
 // TMEM -> ReLU/bf16 -> st.shared only (the 64 LDS.128 + 64 FADD2 per row and layer it replaces cost 11 % of the kernel).
+#include <cuda.h>            // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
 #include "engine.h"
 #include "tc_common.cuh"
 #include "rows.cuh"
@@ -230,14 +231,25 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
   }
 }
 
+// TMA tile load of this CTA's half of a weight stage (rows [row0, row0 + box rows) of the packed image seen as a
+// [rows x 64] bf16 matrix) that completes on an mbarrier of EITHER CTA of the pair (.cta_group::2): both halves signal the
+// leader's w_full directly.  A plain cp.async.bulk can only signal a barrier of its destination CTA, so the peer's arrival
+// had to be relayed by a forwarder warp (peer barrier -> poll -> remote arrive): that hop sat on the ring's round trip.
+__device__ __forceinline__ void tma_stage_cg2(void* smem_dst, const CUtensorMap* tmap, int row0, uint32_t mbar_cluster_addr) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(tmap), "r"(0), "r"(row0), "r"(mbar_cluster_addr)
+               : "memory");
+}
+
 // SAVE: training forward -- every A-operand block (PE, h_0..h_7, feature, PE(dir), view hidden) is also written to the
 // activation arena straight from the epilogue registers (coalesced st.global.v4 in the arena's core-matrix order,
 // tc_arena.cuh), together with the ReLU bit masks the dgrad chain needs.  (Bulk shared->global stores of the same
 // blocks cost 40 % of the kernel: their shared-memory reads compete with the MMA operand fetch.)
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16* __restrict__ wpack,
-                       const uint8_t* __restrict__ wbias, const float* __restrict__ P, int64_t M, int64_t n_pair,
+mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64, int stage_row0,
+                       RowSrc src, float4* __restrict__ raw, const uint8_t* __restrict__ wbias, const float* __restrict__ P, int64_t M, int64_t n_pair,
                        uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if (!SAVE && src.row_count) {      // compacted row list (fast_sampling work skipping): the row count lives on the device
@@ -254,7 +266,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
 
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA12, smem_u32(smem));   // swizzle-128B needs 1024B alignment
   if (tid == 0) {
-    for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
+    for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], 1); mbar_init(&sb.w_empty[i], 1); }   // w_full: used in the leader only
     for (int i = 0; i < kBiasRing; ++i) { mbar_init(&sb.b_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.b_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
     fence_barrier_init();
@@ -276,6 +288,7 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     // ===== weight producer (both CTAs): my half of every stage =====
     if (lane == 0) {
       uint32_t it = 0, itb = 0;
+      const uint32_t w_full_leader = mapa_u32(smem_u32(&sb.w_full[0]), 0);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li) {
           const uint32_t bytes = (uint32_t)sched_n(li) * 64u;                 // half of the stage: N/2 rows x 128 B
@@ -290,9 +303,10 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
             for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
               mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
-              const uint8_t* gsrc = reinterpret_cast<const uint8_t*>(wpack) + (size_t)(sched_start(li) + kb) * kStageImage + (size_t)rank * bytes;
-              mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
-              bulk_g2s(smem + kOffW + slot * kHalfBytes, gsrc, bytes, &sb.w_full[slot]);
+              // both halves complete on the leader's barrier, which expects the bytes of the pair
+              if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
+              tma_stage_cg2(smem + kOffW + slot * kHalfBytes, sched_n(li) == 256 ? &tm128 : &tm64,
+                            stage_row0 + (sched_start(li) + kb) * 256 + (int)rank * (sched_n(li) / 2), w_full_leader + slot * 8u);
             }
           }
         }
@@ -300,9 +314,9 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
     }
     __syncwarp();
   } else if (warp == 1 && rank == 1) {
-    // ===== forwarder (peer CTA): relay local weight arrival to the leader's w_full =====
+    // ===== forwarder (peer CTA): relay the arrival of my half of a bias slab to the leader's b_full =====
     if (lane == 0) {
-      uint32_t it = 0, itb = 0;
+      uint32_t itb = 0;
       for (int64_t st = pair0; st < n_pair; st += pair_stride)
         for (int li = 0; li < kNumSched; ++li)
           for (int rep = 0; rep < kReps; ++rep) {
@@ -310,11 +324,6 @@ mlp_tc2_forward_kernel(RowSrc src, float4* __restrict__ raw, const __nv_bfloat16
             ++itb;
             mbar_wait(&sb.b_full[bslot], bpar, 0x58 + bslot);
             mbar_arrive_remote(mapa_u32(smem_u32(&sb.b_full[bslot]), 0));
-            for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
-              const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-              mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
-              mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
-            }
           }
     }
     __syncwarp();
@@ -503,10 +512,33 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   const int64_t n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
   const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
-  const __nv_bfloat16* wp = h->wpack + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
+  // tensor maps over the packed stage images of both nets: [2 * 39 * 256 rows x 64 bf16] (rows of 128 bytes, already
+  // swizzled by the packer, so the map copies them verbatim); boxes of 128 rows (N = 256 layers) and 64 rows (view layer)
+  struct Maps { const void* base = nullptr; CUtensorMap tm128, tm64; };
+  static Maps maps_dev[64];
+  Maps& mp = maps_dev[h->device & 63];
+  if (mp.base != h->wpack) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                 const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
+      return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled not available");
+    const cuuint64_t gdim[2] = {64, (cuuint64_t)2 * kNumStages * 256}, gstride[1] = {128};
+    const cuuint32_t estr[2] = {1, 1};
+    for (int v = 0; v < 2; ++v) {
+      const cuuint32_t box[2] = {64, v == 0 ? 128u : 64u};
+      CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &mp.tm128 : &mp.tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)h->wpack, gdim, gstride, box, estr,
+                                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled failed");
+    }
+    mp.base = h->wpack;
+  }
+  const int stage_row0 = (net == NERF_NET_FINE ? 1 : 0) * kNumStages * 256;
   const uint8_t* wb = reinterpret_cast<const uint8_t*>(h->wpack) + tc_wpack_bias_offset() + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumSched * kBiasSlabBytes;
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, wb, P, M, n_pair, act_arena);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(src, reinterpret_cast<float4*>(raw), wp, wb, P, M, n_pair, nullptr);
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(mp.tm128, mp.tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(mp.tm128, mp.tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));
