@@ -329,7 +329,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
     __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA) =====
-    if (lane == 0) {
+    {                                   // the whole warp, converged: see umma_ss2_w
       uint32_t it = 0, itb = 0, lc = 0;
       const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE), sW = smem_u32(smem + kOffW);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
@@ -340,7 +340,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
           auto a_block = [&](int kb) { return li == 0 ? -1 : li == 5 ? kb - 1 : li == 9 ? (kb < 4 ? kb : -1) : kb; };
           // bias slab: one K = 16 MMA (un-swizzled K-major operands) that also initialises the accumulator
           auto issue_bias = [&](int tile, uint32_t bslot) {
-            umma_ss2(tmem + tile * 256u, make_smem_desc(smem_u32(smem + kOffBias), 128, 256, kLayoutNone),
+            umma_ss2_w(tmem + tile * 256u, make_smem_desc(smem_u32(smem + kOffBias), 128, 256, kLayoutNone),
                      make_smem_desc(smem_u32(smem + kOffBiasRing) + bslot * 4096u, 128, 256, kLayoutNone), idesc, 0u);
           };
           auto issue = [&](int tile, int kb, uint32_t slot) {
@@ -349,7 +349,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
             const uint32_t b_base = sW + slot * kHalfBytes;
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
-              umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
+              umma_ss2_w(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
                        make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, 1u);
             }
           };
@@ -366,16 +366,16 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
                 mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
                 tc_fence_after();
                 issue_bias(tile, bslot);
-                umma_commit2(&sb.b_empty[bslot], 0x3);
+                umma_commit2_w(&sb.b_empty[bslot], 0x3);
               }
               for (int kb = 0; kb < nkb; ++kb, ++it) {
                 const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
                 mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
                 tc_fence_after();
                 issue(tile, kb, slot);
-                umma_commit2(&sb.w_empty[slot], 0x3);
+                umma_commit2_w(&sb.w_empty[slot], 0x3);
               }
-              umma_commit2(&sb.acc_full[tile], 0x3);
+              umma_commit2_w(&sb.acc_full[tile], 0x3);
             }
           } else {
             // Render: every weight stage feeds both tiles before it is released (half the weight traffic; with the
@@ -391,7 +391,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
                 tc_fence_after();
                 issue_bias(tile, bslot);
               }
-              umma_commit2(&sb.b_empty[bslot], 0x3);
+              umma_commit2_w(&sb.b_empty[bslot], 0x3);
             }
             for (int kb = 0; kb < nkb; ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
@@ -400,9 +400,9 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
 #pragma unroll
               for (int tile = 0; tile < 2; ++tile) {
                 issue(tile, kb, slot);
-                if (kb == nkb - 1) umma_commit2(&sb.acc_full[tile], 0x3);
+                if (kb == nkb - 1) umma_commit2_w(&sb.acc_full[tile], 0x3);
               }
-              umma_commit2(&sb.w_empty[slot], 0x3);
+              umma_commit2_w(&sb.w_empty[slot], 0x3);
             }
           }
         }

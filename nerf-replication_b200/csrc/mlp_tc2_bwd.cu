@@ -277,7 +277,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer (leader) =====
-    if (lane == 0) {
+    {                                   // the whole warp, converged: see umma_ss2_w (tc_common.cuh)
       uint32_t it = 0, lc = 0;
       const uint32_t sA = smem_u32(smem + kOffA), sW = smem_u32(smem + kOffW);
       for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
@@ -298,11 +298,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
               const uint32_t b_base = sW + slot * kHalfBytes;
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_ss2(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
+                umma_ss2_w(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
                          make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
-              umma_commit2(&sb.w_empty[slot], 0x3);
+              umma_commit2_w(&sb.w_empty[slot], 0x3);
             }
-            umma_commit2(&sb.acc_full[tile], 0x3);
+            umma_commit2_w(&sb.acc_full[tile], 0x3);
           }
         }
     }
@@ -585,7 +585,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer: D[256 x (256 | 128)] += dZ^T X, 4 K-steps of 16 rows per half tile =====
-    if (lane == 0) {
+    {                                   // the whole warp, converged: see umma_ss2_w (tc_common.cuh)
       uint32_t it = 0, uc = 0;
       const uint32_t idesc_main = make_idesc_bf16(256, 256, 1, 1), idesc_extra = make_idesc_bf16(256, 128, 1, 1);
       for (int u = pair0; u < a.n_units; u += pair_stride, ++uc) {
@@ -606,12 +606,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             const uint32_t acc = (it > it0 || ks > 0) ? 1u : 0u;
             const uint64_t ad = make_smem_desc(base + ks * 256, 128, 1024, kLayoutNone);
             if (jb.main_slot >= 0)
-              umma_ss2(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_main, acc);
-            umma_ss2(tmem + 256, ad, make_smem_desc(xbase + ks * 256, 128, 1024, kLayoutNone), idesc_extra, acc);
+              umma_ss2_w(tmem, ad, make_smem_desc(base + 2 * kPiece + ks * 256, 128, 1024, kLayoutNone), idesc_main, acc);
+            umma_ss2_w(tmem + 256, ad, make_smem_desc(xbase + ks * 256, 128, 1024, kLayoutNone), idesc_extra, acc);
           }
-          umma_commit2(&sb.empty[slot], 0x3);
+          umma_commit2_w(&sb.empty[slot], 0x3);
         }
-        umma_commit2(&sb.acc_done, 0x3);
+        umma_commit2_w(&sb.acc_done, 0x3);
       }
     }
     __syncwarp();
