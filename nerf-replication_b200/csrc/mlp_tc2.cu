@@ -378,31 +378,39 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
               umma_commit2_w(&sb.acc_full[tile], 0x3);
             }
           } else {
-            // Render: every weight stage feeds both tiles before it is released (half the weight traffic; with the
-            // 3-slot ring the per-tile order above starves the tensor pipe: 1075 vs 1128 TFLOP/s measured).
-            {
-              const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
-              ++itb;
-              mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
-              tc_fence_after();
-#pragma unroll
-              for (int tile = 0; tile < 2; ++tile) {
-                mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
-                tc_fence_after();
-                issue_bias(tile, bslot);
-              }
-              umma_commit2_w(&sb.b_empty[bslot], 0x3);
-            }
+            // Render: every weight stage feeds both tiles before it is released (half the weight traffic of the per-tile
+            // order, which starves on the ring's round trip).  Tile X runs one operation ahead of tile Y (bias MMA, then the
+            // k-blocks): X's accumulator is complete -- and its epilogue starts -- one k-block earlier, and its first MMAs
+            // of the next layer run under the tail of Y's epilogue instead of waiting for it.
+            const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
+            ++itb;
+            mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
+            tc_fence_after();
+            mbar_wait(&sb.act_ready[0], lc & 1u, 0x30);
+            tc_fence_after();
+            issue_bias(0, bslot);
             for (int kb = 0; kb < nkb; ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
               mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+              tc_fence_after();
+              issue(0, kb, slot);
+              if (kb == nkb - 1) umma_commit2_w(&sb.acc_full[0], 0x3);
+              if (kb == 0) {
+                mbar_wait(&sb.act_ready[1], lc & 1u, 0x31);
                 tc_fence_after();
-#pragma unroll
-              for (int tile = 0; tile < 2; ++tile) {
-                issue(tile, kb, slot);
-                if (kb == nkb - 1) umma_commit2_w(&sb.acc_full[tile], 0x3);
+                issue_bias(1, bslot);
+                umma_commit2_w(&sb.b_empty[bslot], 0x3);
+              } else {
+                const uint32_t pslot = (it - 1) % kRing;
+                issue(1, kb - 1, pslot);
+                umma_commit2_w(&sb.w_empty[pslot], 0x3);
               }
-              umma_commit2_w(&sb.w_empty[slot], 0x3);
+            }
+            {
+              const uint32_t pslot = (it - 1) % kRing;
+              issue(1, nkb - 1, pslot);
+              umma_commit2_w(&sb.acc_full[1], 0x3);
+              umma_commit2_w(&sb.w_empty[pslot], 0x3);
             }
           }
         }
