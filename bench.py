@@ -47,8 +47,8 @@ def measured_hbm():
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one launch (the fine-net launch of each class), from the committed
-# ncu --set full captures: profiles/mlp_r1h_metrics.txt (render) and profiles/train_r1d_metrics.txt (training step)
-NCU_TRAFFIC_BYTES = {"render": {"fwd": 53.84e6 + 146.98e6},
+# ncu --set full captures: profiles/mlp_r1j_metrics.txt (render) and profiles/train_r1d_metrics.txt (training step)
+NCU_TRAFFIC_BYTES = {"render": {"fwd": 56.38e6 + 145.70e6},
                      "train": {"fwd": 0.0021e9 + 1.0045e9, "dgrad": 0.0596e9 + 0.9499e9, "wgrad": 1.9247e9 + 0.0039e9}}
 
 
