@@ -116,6 +116,9 @@ void launch_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, f
 // cancels catastrophically at sigma delta ~ 1e-3, so 1 ulp of exp is 1e-4 relative in the sampling pdf.
 __device__ __forceinline__ float exp_cr(float x) { return (float)exp((double)x); }
 __device__ __forceinline__ float sigmoid_cr(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, exp_cr(-x))); }
+// colours: sigmoid is well conditioned (no cancellation), MUFU.EX2 accuracy (|err| < 4e-7 for |x| < 20) is far inside the
+// 1e-5 gate; three of the four double-precision exp calls per sample of the forward composite go away
+__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 struct AlphaQ { float alpha, q, e, delta; };
 __device__ __forceinline__ AlphaQ alpha_q(float sigma, float t_i, float t_next, bool last) {
   AlphaQ r;
@@ -155,9 +158,9 @@ __global__ void composite_kernel(const float4* __restrict__ raw, const float* __
       carry *= __shfl_sync(0xffffffffu, incl, 31);
       const float w = valid ? T * a.alpha : 0.f;
       if (weights && valid) weights[ray * S + i] = w;
-      sr += w * sigmoid_cr(v.x);
-      sg += w * sigmoid_cr(v.y);
-      sb += w * sigmoid_cr(v.z);
+      sr += w * sigmoid_fast(v.x);
+      sg += w * sigmoid_fast(v.y);
+      sb += w * sigmoid_fast(v.z);
       sd += w * ti;
       sa += w;
     }
