@@ -8,14 +8,16 @@
 // so per SM the weight traffic, the weight ring and the B-operand bandwidth are halved.
 //
 // Per CTA (cluster = 2 CTAs on one TPC, persistent over "pair super-tiles" of 512 rows; a CTA owns 256 of them
-// as two 128-row tiles X, Y that ping-pong between MMA and epilogue):
+// as two 128-row tiles X, Y):
 //   warp 0      weight producer: this CTA's half of every stage image (16 KB: 128 weight rows x 64 k, bf16,
-//               128B-swizzled) via cp.async.bulk into a 3-deep ring, completion on mbarriers
-//   warp 1      rank 0: MMA issuer -- one lane issues tcgen05.mma.cta_group::2 (M=256, N=256|128, K=16) for X
-//               then Y on every stage; tcgen05.commit multicast to both CTAs' barriers
-//               rank 1: forwarder -- relays "my half of the stage has landed" to the leader's barrier
+//               128B-swizzled by the packer) by 2-SM TMA tile loads into a 3-deep ring; both halves complete on the
+//               LEADER's mbarrier (.cta_group::2); bias slabs (4 KB) by cp.async.bulk into their own 2-slot ring
+//   warp 1      rank 0: MMA issuer -- the warp runs converged, one elected lane issues tcgen05.mma.cta_group::2
+//               (M=256, N=256|128, K=16); tcgen05.commit multicast to both CTAs' barriers.  Render: every stage feeds X
+//               then Y, X one operation ahead; training: one tile's whole layer, then the other's
+//               rank 1: forwarder -- relays "my half of the bias slab has landed" to the leader's barrier
 //               both: TMEM allocation (cta_group::2, 512 columns: X accumulators [0,256), Y [256,512))
-//   warps 2-5   tile X: positional encoding -> bf16 A operand; per layer TMEM -> +bias (shared memory), ReLU ->
+//   warps 2-5   tile X: positional encoding (computed ahead, under the MMAs) -> bf16 A operand; per layer TMEM -> ReLU ->
 //               bf16 -> A operand of the next layer (in place); sigma / rgb heads on CUDA cores
 //   warps 6-9   same for tile Y
 // Shared memory (bytes): A_X 64K | A_Y 64K | PE_X 16K | PE_Y 16K | W ring 3 x 16K | ones slab 4K | bias ring 2 x 4K | heads 2.5K | barriers
@@ -41,7 +43,7 @@ constexpr int kHalfBytes = 16384;               // this CTA's half of a 256-row 
 constexpr int kRing = 3;
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
 constexpr int kNumStages = 39;
-constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
+constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 168 registers per thread
 constexpr int kOnesBytes = 4096;                // constant A slab of the bias MMA: 128 rows x 16 k, columns 0..2 = 1.0
 constexpr int kBiasSlabBytes = 8192;            // packed bias slab of one schedule entry (both halves), mlp_tc.cu pack_bias_slabs_kernel
 constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
@@ -70,17 +72,6 @@ struct Bars {
 __device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk, uint32_t a,
                                             uint32_t b, uint32_t c, uint32_t d) {
   *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
-}
-
-// packed fp32x2 add (FADD2 on sm_100): {a0,a1} += {b0,b1}
-__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
-  asm("{\n\t.reg .b64 ra, rb;\n\t"
-      "mov.b64 ra, {%0, %1};\n\t"
-      "mov.b64 rb, {%2, %3};\n\t"
-      "add.rn.f32x2 ra, ra, rb;\n\t"
-      "mov.b64 {%0, %1}, ra;\n\t}"
-      : "+f"(a0), "+f"(a1)
-      : "f"(b0), "f"(b1));
 }
 
 // sin / cos of (x * 2^k) for the bf16 A operand: x * 2^k / (2 pi) is reduced to [-0.5, 0.5] turns with a two-term
