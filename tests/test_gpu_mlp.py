@@ -112,6 +112,32 @@ def test_mlp_forward_tcgen05_vs_oracle(oracle, sharp, R, S):
     eng.close()
 
 
+def test_mlp_biases_enter_the_gemm_at_fp32_accuracy(oracle):
+    """The bf16 kernel adds no bias in its epilogue: every layer starts with one K = 16 MMA on a bias slab whose rows hold
+    the bias split into three bf16 terms (csrc/mlp_tc.cu pack_bias_slabs_kernel).  With all trunk weights zero the
+    activations are the (ReLU'd) biases themselves, and the two CUDA-core heads, which read the fp32 accumulator values,
+    return plain sums of them: sigma = sum relu(b_7) + b_alpha, rgb = sum relu(b_views) + b_rgb with unit head weights.
+    A bias that reached the accumulator as a single bf16 (2^-9 relative) would miss the float64 sums by ~1e-3 relative."""
+    g = torch.Generator().manual_seed(11)
+    sd = {k: torch.zeros_like(v) for k, v in oracle.init_state_dict(0).items()}
+    for k in sd:
+        if k.endswith("bias"):
+            sd[k] = torch.randn(sd[k].shape, generator=g) * 1.7 + 0.3          # nothing here is bf16-representable
+        if "alpha_linear.weight" in k or "rgb_linear.weight" in k:
+            sd[k] = torch.ones_like(sd[k])
+    eng = make_engine(oracle, sd, "bf16")
+    pts = (torch.rand(9, 37, 3, generator=g) - 0.5) * 6.0
+    vd = torch.nn.functional.normalize(torch.randn(9, 3, generator=g), dim=-1)
+    for which, prefix in ((0, "model."), (1, "model_fine.")):
+        raw = eng.mlp_forward(which, pts.cuda(), vd.cuda()).cpu().double()
+        sig = float(sd[prefix + "pts_linears.7.bias"].double().clamp(min=0).sum() + sd[prefix + "alpha_linear.bias"].double())
+        hv = float(sd[prefix + "views_linears.0.bias"].double().clamp(min=0).sum())
+        rgb = torch.tensor([hv + float(b) for b in sd[prefix + "rgb_linear.bias"].double()], dtype=torch.float64)
+        assert float((raw[..., 3] - sig).abs().max()) <= 2e-6 * abs(sig), (float(raw[0, 0, 3]), sig)
+        assert float((raw[..., :3] - rgb).abs().max()) <= 2e-6 * float(rgb.abs().max()), (raw[0, 0, :3], rgb)
+    eng.close()
+
+
 def test_mlp_forward_tcgen05_masked_and_multi_tile(oracle):
     """More rows than one wave of 256-row super-tiles per SM (persistent loop), ragged tail, mask."""
     sd, pts, vd = _bf16_case(oracle, False, 1203, 64, 5)      # 76 992 rows = 300.75 super-tiles
