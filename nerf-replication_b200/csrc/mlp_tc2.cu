@@ -38,7 +38,7 @@ namespace v2 {
 constexpr int kTile = 128;
 constexpr int kRowsPerCta = 2 * kTile;          // X + Y
 constexpr int kRowsPerPair = 2 * kRowsPerCta;   // 512
-constexpr int kStageImage = 32768;              // packed stage image (both halves), see mlp_tc.cu pack_weights_kernel
+// (a packed stage image is 256 rows x 128 B = 32 KB, both halves: mlp_tc.cu pack_weights_kernel; the tensor maps address it by rows)
 constexpr int kHalfBytes = 16384;               // this CTA's half of a 256-row stage (views layer: 8192)
 constexpr int kRing = 3;
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS

@@ -25,7 +25,7 @@ using namespace tc;
 namespace bw {
 
 constexpr int kTile = 128;
-constexpr int kRowsPerCta = 256, kRowsPerPair = 512;
+constexpr int kRowsPerPair = 512;
 constexpr int kStageImage = 32768;
 constexpr int kHalfBytes = 16384;
 constexpr int kRing = 6;        // weight stages in flight
