@@ -16,6 +16,10 @@ struct NerfEngine {
   __nv_bfloat16* wpack = nullptr;  // packed bf16 weight images for the tcgen05 kernels
   size_t wpack_bytes = 0;
   __nv_bfloat16* wpack_bwd = nullptr;   // transposed stage images for the dgrad chain (mlp_tc2_bwd.cu)
+  // tensor maps (CUtensorMap, 128 bytes each) over the packed stage images for the 2-SM TMA weight loads of mlp_tc2.cu:
+  // boxes of 128 / 64 rows; encoded for tmap_base == wpack
+  alignas(64) unsigned char tmaps[2][128] = {};
+  const void* tmap_base = nullptr;
   bool params_set = false;
   int tc_variant = 2;              // 2 = CTA-pair kernel (mlp_tc2.cu), 1 = single-CTA kernel (mlp_tc.cu); env NERF_TC_VARIANT
 

@@ -513,10 +513,10 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   // tensor maps over the packed stage images of both nets: [2 * 39 * 256 rows x 64 bf16] (rows of 128 bytes, already
   // swizzled by the packer, so the map copies them verbatim); boxes of 128 rows (N = 256 layers) and 64 rows (view layer)
-  struct Maps { const void* base = nullptr; CUtensorMap tm128, tm64; };
-  static Maps maps_dev[64];
-  Maps& mp = maps_dev[h->device & 63];
-  if (mp.base != h->wpack) {
+  static_assert(sizeof(CUtensorMap) == sizeof(h->tmaps[0]), "CUtensorMap size");
+  CUtensorMap& tm128 = *reinterpret_cast<CUtensorMap*>(h->tmaps[0]);
+  CUtensorMap& tm64 = *reinterpret_cast<CUtensorMap*>(h->tmaps[1]);
+  if (h->tmap_base != h->wpack) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
     void* fn = nullptr;
@@ -527,17 +527,17 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
     const cuuint32_t estr[2] = {1, 1};
     for (int v = 0; v < 2; ++v) {
       const cuuint32_t box[2] = {64, v == 0 ? 128u : 64u};
-      CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &mp.tm128 : &mp.tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)h->wpack, gdim, gstride, box, estr,
+      CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &tm128 : &tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)h->wpack, gdim, gstride, box, estr,
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       if (r != CUDA_SUCCESS) return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled failed");
     }
-    mp.base = h->wpack;
+    h->tmap_base = h->wpack;
   }
   const int stage_row0 = (net == NERF_NET_FINE ? 1 : 0) * kNumStages * 256;
   const uint8_t* wb = reinterpret_cast<const uint8_t*>(h->wpack) + tc_wpack_bias_offset() + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumSched * kBiasSlabBytes;
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(mp.tm128, mp.tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, act_arena);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(mp.tm128, mp.tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, nullptr);
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));
