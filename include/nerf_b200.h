@@ -149,11 +149,20 @@ int nerf_forward_backward(NerfEngine* h, const float* rays_o, const float* rays_
 /* Split form used by the autograd drop-in (Renderer.render under torch.enable_grad()): the forward keeps
  * its activations inside the handle until the matching backward.  d_rgb [n,3] / d_depth [n] are the incoming
  * gradients of the maps (either may be NULL); gradients are accumulated into flat_grad (zeroed first when
- * zero_grad != 0). */
+ * zero_grad != 0).  The handle keeps the activations of ONE forward: *forward_id (host, may be NULL) identifies it, and
+ * nerf_train_backward fails with NERF_E_STATE when its forward_id (0 = do not check) is no longer the latest forward. */
 int nerf_train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
-                       const float* u, float* rgb, float* depth, void* stream);
+                       const float* u, float* rgb, float* depth, uint64_t* forward_id, void* stream);
 int nerf_train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
-                        const float* d_depth, float* flat_grad, int zero_grad, void* stream);
+                        const float* d_depth, float* flat_grad, int zero_grad, uint64_t forward_id, void* stream);
+/* Data-parallel hook (DistributedDataParallel's overlapped gradient reduction, src/train/trainers/trainer.py:16-21): the
+ * fine net's half of flat_grad ([NERF_PARAMS_PER_NET, NERF_PARAMS_TOTAL)) is final before the coarse net's backward starts.
+ * Makes `stream` wait for that point of the last nerf_forward_backward / nerf_train_backward / nerf_bank_train_step issued
+ * on this handle, so that a collective on that half can overlap the rest of the backward pass. */
+int nerf_stream_wait_fine_grads(NerfEngine* h, void* stream);
+/* nerf_forward_backward / nerf_bank_train_step replay their launches as one CUDA graph from the third identical call on
+ * (default on; off = plain stream launches, e.g. under a per-kernel profiler). */
+int nerf_set_graph_mode(NerfEngine* h, int on);
 /* g = clamp(g,-clip,clip) (clip<=0: off); torch.optim.Adam step `step` (1-based), weight_decay 0;
  * updates flat_param/m/v in place and refreshes the engine's packed bf16 weights. */
 int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* flat_grad, float* m, float* v,
@@ -194,11 +203,8 @@ int nerf_eval_image(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, i
 int nerf_eval_ssim(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int H, int W, int win_size, double* ssim_sum_out,
                    void* stream);
 
-/* ---- debug / bring-up ------------------------------------------------------------------------------ */
-/* tcgen05 descriptor probe battery (see csrc/probe.cu); writes results for `variant` into out[]. */
-int nerf_debug_umma_probe(int variant, const float* a, const float* b, float* d, int M, int N, int K,
-                          void* stream);
-
+/* ---- debug ------------------------------------------------------------------------------------------
+ * (the tcgen05 descriptor probe battery of the bring-up lives in its own library: include/nerf_b200_probe.h) */
 /* watchdog record of the tcgen05 kernels: a barrier that never completes traps the kernel instead of
  * hanging the GPU and leaves {tag, blockIdx, threadIdx, parity, ...} here.  out8: 64 uint32 (host): [0,8) first record,
  * [8,64) one word per stuck waiter (tag | warp << 12 | block << 16 | parity << 31). */

@@ -50,8 +50,10 @@ SIGNATURES = {
     "nerf_render_camera": (_I, [_P, C.POINTER(_D), _I, _I, _D, _D, _D, _L, _L, C.POINTER(NerfRenderOut), _P]),
     "nerf_render_rays_host": (_I, [_P, _P, _P, _L, _P, _P]),
     "nerf_forward_backward": (_I, [_P, _P, _P, _P, _L, _P, _P, _F, _P, _P, _P, _P]),
-    "nerf_train_forward": (_I, [_P, _P, _P, _L, _P, _P, _P, _P, _P]),
-    "nerf_train_backward": (_I, [_P, _P, _P, _L, _P, _P, _P, _I, _P]),
+    "nerf_train_forward": (_I, [_P, _P, _P, _L, _P, _P, _P, _P, C.POINTER(C.c_uint64), _P]),
+    "nerf_train_backward": (_I, [_P, _P, _P, _L, _P, _P, _P, _I, C.c_uint64, _P]),
+    "nerf_stream_wait_fine_grads": (_I, [_P, _P]),
+    "nerf_set_graph_mode": (_I, [_P, _I]),
     "nerf_clip_adam": (_I, [_P, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I, _P]),
     "nerf_bank_create": (_I, [_P, _I, _I, _I, _D, _D, _D, _I, C.POINTER(_I)]),
     "nerf_bank_destroy": (_I, [_P, _I]),
@@ -61,12 +63,16 @@ SIGNATURES = {
     "nerf_bank_train_step": (_I, [_P, _I, _I, _I, _P, _L, C.c_uint64, _L, _P, _P, _F, _P, _P, _P, _P]),
     "nerf_eval_image": (_I, [_P, _P, _P, _L, _P, _P, _P]),
     "nerf_eval_ssim": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
-    "nerf_debug_umma_probe": (_I, [_I, _P, _P, _P, _I, _I, _I, _P]),
     "nerf_debug_tc_watchdog": (_I, [C.POINTER(C.c_uint)]),
     "nerf_debug_waitprof": (_I, [_I, C.POINTER(C.c_ulonglong)]),
 }
 
+# include/nerf_b200_probe.h: the bring-up probe battery, a separate library (not part of the product .so)
+PROBE_LIB_PATH = os.path.join(HERE, "libnerf_b200_probe.so")
+PROBE_SIGNATURES = {"nerf_debug_umma_probe": (_I, [_I, _P, _P, _P, _I, _I, _I, _P])}
+
 _lib = None
+_probe = None
 
 
 def load():
@@ -83,3 +89,17 @@ def load():
         fn.restype, fn.argtypes = res, args
     _lib = lib
     return lib
+
+
+def load_probe():
+    """Loads libnerf_b200_probe.so (tests only)."""
+    global _probe
+    if _probe is None:
+        if not os.path.exists(PROBE_LIB_PATH):
+            raise RuntimeError("libnerf_b200_probe.so is missing (%s): run `python nerf-replication_b200/build.py`" % PROBE_LIB_PATH)
+        lib = C.CDLL(PROBE_LIB_PATH)
+        for name, (res, args) in PROBE_SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _probe = lib
+    return _probe

@@ -1,18 +1,29 @@
-"""Builds libnerf_b200.so in-tree with nvcc for sm_100a (no torch extension machinery: the library is a
-plain C-ABI shared object; Python binds it with ctypes).  `python nerf-replication_b200/build.py`."""
+"""Builds the engine in-tree with nvcc for sm_100a (no torch extension machinery: plain C-ABI shared objects; Python binds
+them with ctypes).  `python nerf-replication_b200/build.py [--force]`.
+
+  libnerf_b200.so        the product library (include/nerf_b200.h)
+  libnerf_b200_probe.so  the tcgen05 descriptor probe battery of the bring-up (include/nerf_b200_probe.h; tests only)
+
+`build()` reports on stdout whether each library was COMPILED by this call or REUSED (sources + flags hash unchanged), so a
+driver log shows which of the two happened on a given box.  NERF_B200_REBUILD=1 forces a recompile.
+"""
 import concurrent.futures
 import hashlib
 import os
 import subprocess
 import sys
+import time
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libnerf_b200.so")
+OUT_PROBE = os.path.join(HERE, "libnerf_b200_probe.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "stages.cu", "mlp_fp32.cu", "mlp_tc.cu", "mlp_tc2.cu", "mlp_tc2_bwd.cu", "adam.cu", "bank.cu", "probe.cu"]
+SOURCES = ["api.cu", "stages.cu", "mlp_fp32.cu", "pack_weights.cu", "mlp_tc2.cu", "mlp_tc2_bwd.cu", "adam.cu", "bank.cu"]
+PROBE_SOURCES = ["probe.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-Wno-deprecated-gpu-targets", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
+last_build = {}      # library file name -> "compiled" | "reused" (what the last build() call did)
 
 
 def _nvcc():
@@ -22,32 +33,48 @@ def _nvcc():
     raise RuntimeError("nvcc not found")
 
 
-def _digest():
+def _digest(sources):
+    """Hash of everything a library is built from: its sources, every header next to them, the public headers, the flags."""
     h = hashlib.sha256()
-    for root in (CSRC, os.path.join(os.path.dirname(HERE), "include")):
-        for f in sorted(os.listdir(root)):
-            with open(os.path.join(root, f), "rb") as fh:
+    for f in sorted(os.listdir(CSRC)):
+        if f in sources or not f.endswith(".cu"):
+            with open(os.path.join(CSRC, f), "rb") as fh:
                 h.update(f.encode() + fh.read())
+    inc = os.path.join(os.path.dirname(HERE), "include")
+    for f in sorted(os.listdir(inc)):
+        with open(os.path.join(inc, f), "rb") as fh:
+            h.update(f.encode() + fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()
 
 
-def up_to_date():
-    stamp = OUT + ".stamp"
-    return os.path.exists(OUT) and os.path.exists(stamp) and open(stamp).read() == _digest()
+def up_to_date(out=OUT, sources=SOURCES):
+    stamp = out + ".stamp"
+    return os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == _digest(sources)
 
 
 def build(force=False, verbose=False, waitprof=False):
     """waitprof=True builds the diagnostic flavour libnerf_b200_waitprof.so (-DNERF_TC_WAITPROF: every barrier wait of the
     CTA-pair kernels is timed); select it with NERF_B200_LIB=<path>.  The product library never carries that code."""
     if waitprof:
-        return _build(OUT.replace(".so", "_waitprof.so"), os.path.join(HERE, "build_waitprof"), ["-DNERF_TC_WAITPROF"], verbose, None)
-    if not force and up_to_date():
-        return OUT
-    return _build(OUT, OBJ, [], verbose, OUT + ".stamp")
+        return _build(OUT.replace(".so", "_waitprof.so"), os.path.join(HERE, "build_waitprof"), SOURCES, ["-DNERF_TC_WAITPROF"], verbose)
+    force = force or os.environ.get("NERF_B200_REBUILD") == "1"
+    for out, sources in ((OUT, SOURCES), (OUT_PROBE, PROBE_SOURCES)):
+        name = os.path.basename(out)
+        if not force and up_to_date(out, sources):
+            last_build[name] = "reused"
+            print("[nerf_b200 build] %s: REUSED (sources + flags hash %s... unchanged)" % (name, _digest(sources)[:12]), flush=True)
+            continue
+        t0 = time.time()
+        _build(out, OBJ, sources, [], verbose)
+        with open(out + ".stamp", "w") as f:
+            f.write(_digest(sources))
+        last_build[name] = "compiled"
+        print("[nerf_b200 build] %s: COMPILED %d sources with nvcc for sm_100a in %.1f s" % (name, len(sources), time.time() - t0), flush=True)
+    return OUT
 
 
-def _build(out, objdir, extra, verbose, stamp):
+def _build(out, objdir, sources, extra, verbose):
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
 
@@ -61,14 +88,11 @@ def _build(out, objdir, extra, verbose, stamp):
             print(r.stderr, file=sys.stderr)
         return obj
 
-    with concurrent.futures.ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
-        objs = list(ex.map(compile_one, SOURCES))
+    with concurrent.futures.ThreadPoolExecutor(max_workers=len(sources)) as ex:
+        objs = list(ex.map(compile_one, sources))
     r = subprocess.run([nvcc, "-shared", "-Wno-deprecated-gpu-targets", "-gencode", "arch=compute_100a,code=sm_100a", "-o", out] + objs + ["-lcudart"], capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
-    if stamp:
-        with open(stamp, "w") as f:
-            f.write(_digest())
     return out
 
 

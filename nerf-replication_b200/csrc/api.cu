@@ -4,22 +4,21 @@
 #include <algorithm>
 #include <cstring>
 #include <cstdlib>
+#include <map>
 #include "engine.h"
 #include "tc_arena.cuh"
 
 namespace nerf {
-int tc_debug_read(unsigned int out[8]);
 int tc2_debug_read(unsigned int out[8]);
-void tc1_set_debug_sink(unsigned int*);
 void tc2_set_debug_sink(unsigned int*);
 void tc2b_set_debug_sink(unsigned int*);
-void tcp_set_debug_sink(unsigned int*);
 void tc2_set_debug_sink_waitprof(unsigned long long*);
 void tc2b_set_debug_sink_waitprof(unsigned long long*);
 }
 using namespace nerf;
 
 static std::string g_create_error;
+static void drop_step_graph(NerfEngine* h);
 static unsigned int* g_watchdog_host = nullptr;   // host-mapped, survives a trapped kernel
 
 static int check_cfg(const NerfConfig& c, std::string* why) {
@@ -57,7 +56,7 @@ extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) 
       unsigned int* dp = nullptr;
       if (cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess) {
         g_watchdog_host = hp;
-        tc1_set_debug_sink(dp); tc2_set_debug_sink(dp); tc2b_set_debug_sink(dp); tcp_set_debug_sink(dp);
+        tc2_set_debug_sink(dp); tc2b_set_debug_sink(dp);
       }
     }
     cudaGetLastError();
@@ -66,7 +65,6 @@ extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) 
   h->cfg = *cfg;
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
-  if (const char* v = getenv("NERF_TC_VARIANT")) h->tc_variant = atoi(v) == 1 ? 1 : 2;
   *out = h;
   return NERF_OK;
 }
@@ -75,12 +73,15 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   if (!h) return NERF_OK;
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
+  drop_step_graph(h);
   for (auto& kv : h->ws) if (kv.second.p) cudaFree(kv.second.p);
   for (auto& b : h->banks) { if (b.images) cudaFree(b.images); if (b.poses) cudaFree(b.poses); }
   if (h->wpack) cudaFree(h->wpack);
   if (h->wpack_bwd) cudaFree(h->wpack_bwd);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   if (h->side) cudaStreamDestroy(h->side);
+  if (h->pack_ev) cudaEventDestroy(h->pack_ev);
+  if (h->fine_grad_ev) cudaEventDestroy(h->fine_grad_ev);
   if (h->side_fork) cudaEventDestroy(h->side_fork);
   if (h->side_join) cudaEventDestroy(h->side_join);
   for (int i = 0; i < 2; ++i) {
@@ -110,6 +111,14 @@ static int post(NerfEngine* h, const char* what) {
   return NERF_OK;
 }
 
+// The packed bf16 images are written on the caller's stream; the host-buffer render path runs on the engine's own
+// streams and must not read them before the (re)pack has finished.
+static int record_pack(NerfEngine* h, cudaStream_t st) {
+  if (!h->pack_ev) NERF_CUDA_TRY(h, cudaEventCreateWithFlags(&h->pack_ev, cudaEventDisableTiming));
+  NERF_CUDA_TRY(h, cudaEventRecord(h->pack_ev, st));
+  return NERF_OK;
+}
+
 extern "C" int nerf_set_params(NerfEngine* h, const float* flat, void* stream) {
   if (!h || !flat) return NERF_E_INVALID;
   if (reinterpret_cast<uintptr_t>(flat) & 15) return h->fail(NERF_E_INVALID, "flat parameter buffer must be 16-byte aligned");
@@ -121,9 +130,9 @@ extern "C" int nerf_set_params(NerfEngine* h, const float* flat, void* stream) {
     NERF_CUDA_TRY(h, cudaMemsetAsync(h->wpack, 0, h->wpack_bytes, (cudaStream_t)stream));
   }
   if (!h->wpack_bwd) NERF_CUDA_TRY(h, cudaMalloc(&h->wpack_bwd, tc_bwd_wpack_bytes()));
-  tc_pack_weights(h, flat, h->wpack, (cudaStream_t)stream);
-  tc_pack_dgrad_weights(h, flat, h->wpack_bwd, (cudaStream_t)stream);
+  tc_pack_all(h, flat, h->wpack, h->wpack_bwd, (cudaStream_t)stream);
   h->params_set = true;
+  if (int rc = record_pack(h, (cudaStream_t)stream)) return rc;
   return post(h, "nerf_set_params");
 }
 
@@ -174,7 +183,7 @@ static int run_mlp(NerfEngine* h, int net, const RowSrc& src, float* raw, bool k
     if (rc0) return rc0;
   }
   if (h->profiling) cudaEventRecord(h->prof_event(), st);
-  const int rc = (h->tc_variant == 1 && !keep) ? mlp_tc_forward(h, net, src, raw, st) : mlp_tc2_forward(h, net, src, raw, act, st);
+  const int rc = mlp_tc2_forward(h, net, src, raw, act, st);
   if (h->profiling) { cudaEventRecord(h->prof_event(), st); h->prof_rows += src.R * src.S; h->prof_class.push_back(0); h->prof_class_rows.push_back(src.R * src.S); }
   return rc;
 }
@@ -273,7 +282,7 @@ static uint64_t g_call_counter = 0;
 
 // One chunk of rays through the whole pipeline.  `slot` selects a private workspace (host path ping-pong).
 static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n, const float* jitter, const float* u,
-                        const NerfRenderOut& out, bool keep, int slot, RenderTaps* taps, cudaStream_t st) {
+                        const NerfRenderOut& out, bool keep, int slot, RenderTaps* taps, cudaStream_t st, bool final_composite = true) {
   const NerfConfig& c = h->cfg;
   const int Nc = c.n_samples, Nf = c.n_importance, Nt = Nc + Nf;
   const uint64_t call_id = ++g_call_counter;
@@ -309,7 +318,7 @@ static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n
     // sample has raw = 0, hence weight 0 and relu'(0) = 0: composite_bwd hands the MLP backward an exactly zero d_raw row,
     // which is the reference's autograd through `out[m] = flat` (network.py:238-253) -- no gradient from pruned samples.
     int32_t *row_list = nullptr, *row_count = nullptr;
-    if (c.fast_sampling == 2 && !keep && c.precision == NERF_PRECISION_BF16 && h->tc_variant != 1) {
+    if (c.fast_sampling == 2 && !keep && c.precision == NERF_PRECISION_BF16) {
       char nb[2][32]; snprintf(nb[0], 32, "r%d.rows", slot); snprintf(nb[1], 32, "r%d.nrows", slot);
       if ((rc = h->buf(nb[0], (size_t)n * Nt, &row_list)) || (rc = h->buf(nb[1], 1, &row_count))) return rc;
       NERF_CUDA_TRY(h, cudaMemsetAsync(row_count, 0, sizeof(int32_t), st));
@@ -320,11 +329,11 @@ static int render_chunk(NerfEngine* h, const float* o, const float* d, int64_t n
                                 row_list, row_count))) return rc;
     src.t = tp.t_s; src.S = Nt; src.mask = row_list ? nullptr : prune_mask; src.row_list = row_list; src.row_count = row_count;
     if ((rc = run_mlp(h, NERF_NET_FINE, src, tp.raw_f, keep, st))) return rc;
-    launch_composite(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
+    if (final_composite) launch_composite(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
     if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)
       launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb_coarse, out.depth_coarse, out.acc_coarse, nullptr, st);
   } else {
-    launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
+    if (final_composite) launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb, out.depth, out.acc, nullptr, st);
     if (out.rgb_coarse || out.depth_coarse || out.acc_coarse)
       launch_composite(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, out.rgb_coarse, out.depth_coarse, out.acc_coarse, nullptr, st);
   }
@@ -403,6 +412,8 @@ extern "C" int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, co
     }
   }
   h->pinned_bytes = std::max(h->pinned_bytes, need);
+  // the internal streams start after the last weight (re)pack issued on any caller stream (nerf_set_params / nerf_clip_adam)
+  if (h->pack_ev) for (int i = 0; i < 2; ++i) NERF_CUDA_TRY(h, cudaStreamWaitEvent(h->hs[i], h->pack_ev, 0));
   struct Pending { int64_t r = -1, m = 0; } pend[2];
   auto drain = [&](int s) {   // wait for slot s and copy its maps out of pinned memory
     if (pend[s].r < 0) return;
@@ -447,11 +458,11 @@ extern "C" int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, co
 // graph: fine MLP gets rgb+sigma gradients and an input gradient that flows
 // through PE -> t_fine -> inverse CDF -> coarse weights -> coarse sigma -> coarse trunk.
 static int train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
-                         const float* u, float* rgb, float* depth, cudaStream_t st) {
+                         const float* u, float* rgb, float* depth, bool final_composite, cudaStream_t st) {
   NerfRenderOut out{};
   out.rgb = rgb; out.depth = depth;
   RenderTaps tp;
-  int rc = render_chunk(h, rays_o, rays_d, n, jitter, u, out, true, 9, &tp, st);
+  int rc = render_chunk(h, rays_o, rays_d, n, jitter, u, out, true, 9, &tp, st, final_composite);
   if (rc) { h->taps.n = -1; return rc; }
   h->taps.t_c = tp.t_c; h->taps.raw_c = tp.raw_c; h->taps.t_s = tp.t_s; h->taps.raw_f = tp.raw_f;
   h->taps.sort_idx = tp.sort_idx; h->taps.call_id = tp.call_id; h->taps.n = n; h->taps.jitter = jitter; h->taps.u = u;
@@ -486,8 +497,23 @@ static int mlp_backward(NerfEngine* h, int net, const RowSrc& src, const float* 
   return rc;
 }
 
+// The fine net's half of flat_grad is final here (its wgrad and heads kernels are the last writers): data-parallel callers
+// may start reducing it while the coarse net's backward runs (nerf_stream_wait_fine_grads).
+static int mark_fine_grads(NerfEngine* h, cudaStream_t st) {
+  if (!h->fine_grad_ev) NERF_CUDA_TRY(h, cudaEventCreateWithFlags(&h->fine_grad_ev, cudaEventDisableTiming));
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cs);
+  NERF_CUDA_TRY(h, cudaEventRecordWithFlags(h->fine_grad_ev, st, cs == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault));
+  h->fine_grad_recorded = true;
+  return NERF_OK;
+}
+
+// Backward of the last train_forward.  fused_loss != NULL (nerf_forward_backward): the final pass's composite, the MSE loss
+// and its composite backward are one kernel (d rgb = 2 (rgb - gt) grad_scale / 3n computed per ray), and the coarse composite
+// backward runs inside the sample_pdf backward kernel; otherwise d_rgb / d_depth are the caller's map gradients.
+struct FusedLoss { const float* gt; float scale; float* loss; float* rgb_out; };
 static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
-                          const float* d_depth, float* flat_grad, cudaStream_t st) {
+                          const float* d_depth, const FusedLoss* fl, float* flat_grad, cudaStream_t st) {
   if (h->taps.n != n) return h->fail(NERF_E_STATE, "train_backward: no matching nerf_train_forward");
   const NerfConfig& c = h->cfg;
   const int Nc = c.n_samples, Nf = c.n_importance, Nt = Nc + Nf;
@@ -495,47 +521,111 @@ static int train_backward(NerfEngine* h, const float* rays_o, const float* rays_
   int rc;
   RowSrc src;
   src.rays_o = rays_o; src.rays_d = rays_d; src.R = n;
+  float* sq = nullptr; unsigned int* done = nullptr;
+  if (fl) {
+    const bool fresh = h->ws.find("tr.done") == h->ws.end();
+    if ((rc = h->buf("tr.sq", (size_t)n, &sq)) || (rc = h->buf("tr.done", 1, &done))) return rc;
+    if (fresh) NERF_CUDA_TRY(h, cudaMemsetAsync(done, 0, sizeof(unsigned int), st));
+  }
   if (Nf > 0) {
-    float *d_raw_f, *d_t_s, *d_w_c, *d_raw_c;
+    float *d_raw_f, *d_t_s, *d_raw_c;
     if ((rc = h->buf("tr.d_raw_f", (size_t)n * Nt * 4, &d_raw_f))) return rc;
     if ((rc = h->buf("tr.d_t_s", (size_t)n * Nt, &d_t_s))) return rc;
-    if ((rc = h->buf("tr.d_w_c", (size_t)n * Nc, &d_w_c))) return rc;
     if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
-    launch_composite_bwd(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_f, d_t_s, st);
+    if (fl) launch_composite_loss_bwd(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, fl->gt, fl->scale, fl->rgb_out, d_raw_f, d_t_s, sq, done, fl->loss, st);
+    else launch_composite_bwd(h, tp.raw_f, tp.t_s, n, Nt, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_f, d_t_s, st);
     src.t = tp.t_s; src.S = Nt;
     if ((rc = mlp_backward(h, NERF_NET_FINE, src, d_raw_f, false, flat_grad + NERF_PARAMS_PER_NET, d_t_s, st))) return rc;
+    if ((rc = mark_fine_grads(h, st))) return rc;
     const bool tu = c.train_u != 0;
     if ((rc = launch_sample_pdf_bwd(h, tp.raw_c, tp.t_c, n, Nc, Nf, tu ? tp.u : nullptr, tu && !tp.u, tp.call_id, d_t_s,
-                                    tp.sort_idx, d_w_c, st))) return rc;
-    launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, nullptr, nullptr, d_w_c, d_raw_c, nullptr, st);
+                                    tp.sort_idx, nullptr, st, c.white_bkgd, d_raw_c))) return rc;
     src.t = tp.t_c; src.S = Nc;
     if ((rc = mlp_backward(h, NERF_NET_COARSE, src, d_raw_c, true, flat_grad, nullptr, st))) return rc;
   } else {
     float* d_raw_c;
     if ((rc = h->buf("tr.d_raw_c", (size_t)n * Nc * 4, &d_raw_c))) return rc;
-    launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_c, nullptr, st);
+    if (fl) launch_composite_loss_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, fl->gt, fl->scale, fl->rgb_out, d_raw_c, nullptr, sq, done, fl->loss, st);
+    else launch_composite_bwd(h, tp.raw_c, tp.t_c, n, Nc, c.white_bkgd, d_rgb, d_depth, nullptr, d_raw_c, nullptr, st);
+    if ((rc = mark_fine_grads(h, st))) return rc;     // the fine net is unused: its (zero) half is final from the start
     src.t = tp.t_c; src.S = Nc;
     if ((rc = mlp_backward(h, NERF_NET_COARSE, src, d_raw_c, false, flat_grad, nullptr, st))) return rc;
   }
   return post(h, "train_backward");
 }
 
+extern "C" int nerf_stream_wait_fine_grads(NerfEngine* h, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!h->fine_grad_recorded) return h->fail(NERF_E_STATE, "nerf_stream_wait_fine_grads: no backward pass has been issued on this handle");
+  cudaSetDevice(h->device);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing((cudaStream_t)stream, &cs);
+  NERF_CUDA_TRY(h, cudaStreamWaitEvent((cudaStream_t)stream, h->fine_grad_ev, cs == cudaStreamCaptureStatusActive ? cudaEventWaitExternal : cudaEventWaitDefault));
+  return NERF_OK;
+}
+
 extern "C" int nerf_train_forward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* jitter,
-                                  const float* u, float* rgb, float* depth, void* stream) {
+                                  const float* u, float* rgb, float* depth, uint64_t* forward_id, void* stream) {
   if (!h) return NERF_E_INVALID;
   if (!h->params_set) return h->fail(NERF_E_STATE, "nerf_train_forward before nerf_set_params");
   if (!rays_o || !rays_d || !rgb || n <= 0) return h->fail(NERF_E_INVALID, "nerf_train_forward: bad argument");
   cudaSetDevice(h->device);
-  return train_forward(h, rays_o, rays_d, n, jitter, u, rgb, depth, (cudaStream_t)stream);
+  const int rc = train_forward(h, rays_o, rays_d, n, jitter, u, rgb, depth, true, (cudaStream_t)stream);
+  if (!rc && forward_id) *forward_id = h->taps.call_id;
+  return rc;
 }
 
 extern "C" int nerf_train_backward(NerfEngine* h, const float* rays_o, const float* rays_d, int64_t n, const float* d_rgb,
-                                   const float* d_depth, float* flat_grad, int zero_grad, void* stream) {
+                                   const float* d_depth, float* flat_grad, int zero_grad, uint64_t forward_id, void* stream) {
   if (!h) return NERF_E_INVALID;
   if (!rays_o || !rays_d || !flat_grad || n <= 0 || (!d_rgb && !d_depth)) return h->fail(NERF_E_INVALID, "nerf_train_backward: bad argument");
+  // the handle keeps the activations of ONE forward: a backward for an older forward would silently use the newer one's
+  if (forward_id != 0 && forward_id != h->taps.call_id)
+    return h->fail(NERF_E_STATE, "nerf_train_backward: the activations of this forward were overwritten by a later nerf_train_forward "
+                                 "(one forward, then its backward; the handle keeps one set of activations)");
   cudaSetDevice(h->device);
   if (zero_grad) NERF_CUDA_TRY(h, cudaMemsetAsync(flat_grad, 0, (size_t)NERF_PARAMS_TOTAL * sizeof(float), (cudaStream_t)stream));
-  return train_backward(h, rays_o, rays_d, n, d_rgb, d_depth, flat_grad, (cudaStream_t)stream);
+  return train_backward(h, rays_o, rays_d, n, d_rgb, d_depth, nullptr, flat_grad, (cudaStream_t)stream);
+}
+
+// The whole step body on one stream (also what a CUDA graph of the step captures).
+static int forward_backward_body(NerfEngine* h, const float* rays_o, const float* rays_d, const float* rgb_gt, int64_t n,
+                                 const float* jitter, const float* u, float grad_scale, float* loss, float* flat_grad,
+                                 float* rgb_out, cudaStream_t st) {
+  int rc;
+  NERF_CUDA_TRY(h, cudaMemsetAsync(flat_grad, 0, (size_t)NERF_PARAMS_TOTAL * sizeof(float), st));
+  if ((rc = train_forward(h, rays_o, rays_d, n, jitter, u, nullptr, nullptr, false, st))) return rc;
+  FusedLoss fl{rgb_gt, grad_scale, loss, rgb_out};
+  return train_backward(h, rays_o, rays_d, n, nullptr, nullptr, &fl, flat_grad, st);
+}
+
+// CUDA graph of the step.  Everything the step launches is a pure function of (device pointers, n, config), so the second
+// identical call is captured and later ones replay the graph: ~14 launches become one.  The caller's rays / colours are
+// first copied into engine-owned staging buffers (three small device copies outside the graph) so that callers that
+// rotate their batch tensors still hit the graph.  Falls back to plain launches whenever the step is not replayable:
+// in-kernel Philox randomness (keyed by a per-call counter), profiling brackets, graph mode off.
+struct StepKey {
+  int64_t n; const void *jitter, *u, *loss, *grad, *rgb_out, *params; float scale; NerfConfig cfg;
+  bool operator==(const StepKey& o) const {
+    return n == o.n && jitter == o.jitter && u == o.u && loss == o.loss && grad == o.grad && rgb_out == o.rgb_out && params == o.params &&
+           scale == o.scale && memcmp(&cfg, &o.cfg, sizeof(cfg)) == 0;
+  }
+};
+struct StepGraph { StepKey key{}; bool warm = false; cudaGraphExec_t exec = nullptr; int64_t launches = 0; };
+static std::map<NerfEngine*, StepGraph> g_step_graphs;
+
+static void drop_step_graph(NerfEngine* h) {
+  auto it = g_step_graphs.find(h);
+  if (it == g_step_graphs.end()) return;
+  if (it->second.exec) cudaGraphExecDestroy(it->second.exec);
+  g_step_graphs.erase(it);
+}
+
+extern "C" int nerf_set_graph_mode(NerfEngine* h, int on) {
+  if (!h) return NERF_E_INVALID;
+  h->graph_mode = on != 0;
+  if (!on) drop_step_graph(h);
+  return NERF_OK;
 }
 
 extern "C" int nerf_forward_backward(NerfEngine* h, const float* rays_o, const float* rays_d, const float* rgb_gt, int64_t n,
@@ -546,15 +636,56 @@ extern "C" int nerf_forward_backward(NerfEngine* h, const float* rays_o, const f
   if (!rays_o || !rays_d || !rgb_gt || !loss || !flat_grad || n <= 0) return h->fail(NERF_E_INVALID, "nerf_forward_backward: bad argument");
   cudaSetDevice(h->device);
   cudaStream_t st = (cudaStream_t)stream;
+  const NerfConfig& c = h->cfg;
+  const bool philox = (c.perturb && !jitter) || (c.train_u && !u && c.n_importance > 0);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cs);
+  if (!h->graph_mode || philox || h->profiling || cs != cudaStreamCaptureStatusNone) {
+    return forward_backward_body(h, rays_o, rays_d, rgb_gt, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
+  // stage the inputs (no-op when the caller already uses the staging buffers, e.g. nerf_bank_train_step)
+  float *so, *sd, *sg;
   int rc;
-  float *rgb, *d_rgb;
-  if ((rc = h->buf("tr.rgb", (size_t)n * 3, &rgb))) return rc;
-  if ((rc = h->buf("tr.d_rgb", (size_t)n * 3, &d_rgb))) return rc;
-  NERF_CUDA_TRY(h, cudaMemsetAsync(flat_grad, 0, (size_t)NERF_PARAMS_TOTAL * sizeof(float), st));
-  if ((rc = train_forward(h, rays_o, rays_d, n, jitter, u, rgb, nullptr, st))) return rc;
-  launch_mse_grad(h, rgb, rgb_gt, n, grad_scale, d_rgb, loss, st);
-  if (rgb_out) NERF_CUDA_TRY(h, cudaMemcpyAsync(rgb_out, rgb, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  return train_backward(h, rays_o, rays_d, n, d_rgb, nullptr, flat_grad, st);
+  if ((rc = h->buf("bank.o", (size_t)n * 3, &so)) || (rc = h->buf("bank.d", (size_t)n * 3, &sd)) || (rc = h->buf("bank.c", (size_t)n * 3, &sg))) return rc;
+  const size_t bytes = (size_t)n * 3 * sizeof(float);
+  if (rays_o != so) NERF_CUDA_TRY(h, cudaMemcpyAsync(so, rays_o, bytes, cudaMemcpyDeviceToDevice, st));
+  if (rays_d != sd) NERF_CUDA_TRY(h, cudaMemcpyAsync(sd, rays_d, bytes, cudaMemcpyDeviceToDevice, st));
+  if (rgb_gt != sg) NERF_CUDA_TRY(h, cudaMemcpyAsync(sg, rgb_gt, bytes, cudaMemcpyDeviceToDevice, st));
+  StepKey key{n, jitter, u, loss, flat_grad, rgb_out, h->params, grad_scale, c};
+  StepGraph& sg_ = g_step_graphs[h];
+  if (sg_.exec && sg_.key == key) {
+    NERF_CUDA_TRY(h, cudaGraphLaunch(sg_.exec, st));
+    h->launches += sg_.launches;
+    h->taps.n = -1;                                   // the split-form backward cannot follow a replayed step
+    return NERF_OK;
+  }
+  if (sg_.exec) { cudaGraphExecDestroy(sg_.exec); sg_.exec = nullptr; }
+  if (!(sg_.warm && sg_.key == key)) {
+    // first call with this signature: plain launches (sizes every workspace buffer, sets the kernel attributes)
+    sg_.key = key; sg_.warm = true;
+    return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
+  // second identical call: capture, instantiate, launch
+  const int64_t l0 = h->launches;
+  NERF_CUDA_TRY(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+  rc = forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(st, &graph);
+  if (rc || e != cudaSuccess || !graph) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    sg_.warm = false;
+    h->graph_mode = false;                            // do not try again on this handle
+    if (rc) return rc;
+    return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
+  sg_.launches = h->launches - l0;
+  e = cudaGraphInstantiate(&sg_.exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (e != cudaSuccess) { sg_.exec = nullptr; return h->fail(NERF_E_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
+  NERF_CUDA_TRY(h, cudaGraphLaunch(sg_.exec, st));
+  h->taps.n = -1;
+  return NERF_OK;
 }
 
 extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* flat_grad, float* m, float* v, float lr, float beta1,
@@ -564,10 +695,14 @@ extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* fla
        reinterpret_cast<uintptr_t>(v)) & 15)
     return h->fail(NERF_E_INVALID, "nerf_clip_adam: buffers must be 16-byte aligned");
   cudaSetDevice(h->device);
-  launch_clip_adam(h, flat_param, flat_grad, m, v, NERF_PARAMS_TOTAL, lr, beta1, beta2, eps, clip, step, (cudaStream_t)stream);
   if (h->params_set && flat_param == h->params && h->wpack) {
-    tc_pack_weights(h, flat_param, h->wpack, (cudaStream_t)stream);
-    tc_pack_dgrad_weights(h, flat_param, h->wpack_bwd, (cudaStream_t)stream);
+    // the engine's packed bf16 images follow the masters: update + re-pack in one cooperative launch
+    if (int rc = launch_clip_adam_pack(h, flat_param, flat_grad, m, v, NERF_PARAMS_TOTAL, lr, beta1, beta2, eps, clip, step, h->wpack,
+                                       reinterpret_cast<uint8_t*>(h->wpack) + tc_wpack_bias_offset(), h->wpack_bwd, (cudaStream_t)stream))
+      return rc;
+    if (int rc = record_pack(h, (cudaStream_t)stream)) return rc;
+  } else {
+    launch_clip_adam(h, flat_param, flat_grad, m, v, NERF_PARAMS_TOTAL, lr, beta1, beta2, eps, clip, step, (cudaStream_t)stream);
   }
   return post(h, "nerf_clip_adam");
 }
@@ -597,8 +732,8 @@ extern "C" int nerf_debug_waitprof(int on, unsigned long long* out) {
 // watchdog record of the tcgen05 kernels (valid after a trapped launch); out: 8 uint32
 extern "C" int nerf_debug_tc_watchdog(unsigned int* out8) {
   if (g_watchdog_host && g_watchdog_host[0]) { for (int i = 0; i < 64; ++i) out8[i] = g_watchdog_host[i]; return 0; }
-  unsigned int a[8], b[8];
-  const int r1 = nerf::tc_debug_read(a), r2 = nerf::tc2_debug_read(b);
-  for (int i = 0; i < 8; ++i) out8[i] = b[0] ? b[i] : a[i];
-  return r1 | r2;
+  unsigned int b[8];
+  const int rc = nerf::tc2_debug_read(b);
+  for (int i = 0; i < 8; ++i) out8[i] = b[i];
+  return rc;
 }

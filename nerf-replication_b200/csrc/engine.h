@@ -21,7 +21,6 @@ struct NerfEngine {
   alignas(64) unsigned char tmaps[2][128] = {};
   const void* tmap_base = nullptr;
   bool params_set = false;
-  int tc_variant = 2;              // 2 = CTA-pair kernel (mlp_tc2.cu), 1 = single-CTA kernel (mlp_tc.cu); env NERF_TC_VARIANT
 
   // grow-only named workspace buffers
   struct Buf { void* p = nullptr; size_t bytes = 0; };
@@ -35,6 +34,15 @@ struct NerfEngine {
   // taps of the last training forward (nerf_train_forward), consumed by nerf_train_backward
   struct Taps { float *t_c = nullptr, *raw_c = nullptr, *t_s = nullptr, *raw_f = nullptr; int32_t* sort_idx = nullptr;
                 uint64_t call_id = 0; int64_t n = -1; const float *jitter = nullptr, *u = nullptr; } taps;
+
+  // Ordering of the packed weights against the engine's private streams: recorded on the caller's stream after every
+  // (re)pack (nerf_set_params, nerf_clip_adam); nerf_render_rays_host makes its internal streams wait for it.
+  cudaEvent_t pack_ev = nullptr;
+  // Data-parallel hook: recorded on the caller's stream when the fine net's half of flat_grad is final, i.e. before the
+  // coarse net's backward starts (nerf_stream_wait_fine_grads)
+  cudaEvent_t fine_grad_ev = nullptr;
+  bool fine_grad_recorded = false;
+  bool graph_mode = true;                   // nerf_forward_backward may capture / replay the step as a CUDA graph
 
   // host-path resources (nerf_render_rays_host)
   cudaStream_t side = nullptr;              // forked work that overlaps a persistent kernel (wgrad heads)
@@ -108,10 +116,15 @@ void launch_mse_grad(NerfEngine* h, const float* rgb, const float* gt, int64_t n
 void launch_composite_bwd(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white,
                           const float* d_rgb_map, const float* d_depth_map, const float* d_w, float* d_raw, float* d_t,
                           cudaStream_t st);
-// sample_pdf backward: d_t_sorted [n,Nt] (total gradient at sorted positions) -> d_w_coarse [n,Nc]
+// sample_pdf backward: d_t_sorted [n,Nt] (total gradient at sorted positions) -> d_w_coarse [n,Nc] (may be NULL when
+// d_raw_c is given); d_raw_c != NULL fuses the coarse composite backward behind it (d w -> d_raw_c [n,Nc,4])
 int launch_sample_pdf_bwd(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                           const float* u, bool philox_u, uint64_t call_id, const float* d_t_sorted,
-                          const int32_t* sort_idx, float* d_w_coarse, cudaStream_t st);
+                          const int32_t* sort_idx, float* d_w_coarse, cudaStream_t st, int white = 0, float* d_raw_c = nullptr);
+// fused composite + MSE loss + composite backward of the final pass (training step): see stages.cu
+void launch_composite_loss_bwd(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white, const float* gt,
+                               float scale, float* rgb_out, float* d_raw, float* d_t, float* sq, unsigned int* done, float* loss,
+                               cudaStream_t st);
 
 // ---- mlp_fp32.cu -------------------------------------------------------------------------------
 // Row source for the MLP kernels: either explicit points or rays + depths.
@@ -134,18 +147,17 @@ int mlp_fp32_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, bool
 int mlp_fp32_backward(NerfEngine* h, int net, const RowSrc& src, const float* d_raw, bool coarse_only_sigma,
                       float* flat_grad_net, float* d_t, cudaStream_t st);
 
-// ---- mlp_tc.cu (tcgen05) ------------------------------------------------------------------------
+// ---- pack_weights.cu (bf16 operand images of the tcgen05 forward) ------------------------------------
 size_t tc_wpack_bytes();
 size_t tc_wpack_bias_offset();   // byte offset of the bias slabs ([net][schedule entry] x 8 KB) inside the packed buffer
-void tc_pack_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
-int mlp_tc_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, cudaStream_t st);
+size_t tc_bwd_wpack_bytes();
+// forward stage images + bias slabs (wpack) and the transposed dgrad stage images (wpack_bwd) in one launch
+void tc_pack_all(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, __nv_bfloat16* wpack_bwd, cudaStream_t st);
 
 // ---- mlp_tc2.cu (tcgen05 cta_group::2, CTA pairs; default) ----------------------------------------
 int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8_t* act_arena, cudaStream_t st);
 
 // ---- mlp_tc2_bwd.cu (tensor-core backward) -----------------------------------------------------------
-size_t tc_bwd_wpack_bytes();
-void tc_pack_dgrad_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st);
 int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const float* d_raw, const uint8_t* act_arena,
                   uint8_t* grad_arena, float* pe_scratch, float* d_t, cudaStream_t st);
 
@@ -155,6 +167,9 @@ int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const
 // ---- adam.cu -----------------------------------------------------------------------------------
 void launch_clip_adam(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr,
                       float b1, float b2, float eps, float clip, int step, cudaStream_t st);
+// the same + the re-pack of both bf16 weight images in one cooperative launch (slabs = wpack + tc_wpack_bias_offset())
+int launch_clip_adam_pack(NerfEngine* h, float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2,
+                          float eps, float clip, int step, __nv_bfloat16* wpack, uint8_t* slabs, __nv_bfloat16* wpack_bwd, cudaStream_t st);
 void launch_fill(NerfEngine* h, float* p, int64_t n, float v, cudaStream_t st);
 
 }  // namespace nerf

@@ -18,47 +18,12 @@
 #include "tc_common.cuh"
 #include "rows.cuh"
 #include "tc_arena.cuh"
+#include "pack.cuh"
 
 namespace nerf {
 using namespace tc;
 
 namespace bw {
-
-constexpr int kTile = 128;
-constexpr int kRowsPerPair = 512;
-constexpr int kStageImage = 32768;
-constexpr int kHalfBytes = 16384;
-constexpr int kRing = 6;        // weight stages in flight
-constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
-constexpr int kNumSteps = 11;      // V1, F, L7, L6, PE5, L5, L4, L3, L2, L1, P0
-constexpr int kNumStages = 42;
-enum Step { S_V1 = 0, S_F = 1, S_L7 = 2, S_L6 = 3, S_PE5 = 4, S_L5 = 5, S_L4 = 6, S_L3 = 7, S_L2 = 8, S_L1 = 9, S_P0 = 10 };
-
-__host__ __device__ constexpr int step_nkb(int s) { return s == S_V1 ? 2 : 4; }
-__host__ __device__ constexpr int step_n(int s) { return (s == S_PE5 || s == S_P0) ? 64 : 256; }
-__host__ __device__ constexpr int step_stage0(int s) {
-  int a = 0;
-  for (int i = 0; i < s; ++i) a += step_nkb(i);
-  return a;
-}
-static_assert(step_stage0(kNumSteps) == kNumStages, "dgrad stage count");
-// reference layer whose weight the step multiplies by, and the first input column of that weight it produces
-__host__ __device__ constexpr int step_layer(int s) {
-  return s == S_V1 ? L_VIEWS : s == S_F ? L_FEAT : s == S_L7 ? 7 : s == S_L6 ? 6 : (s == S_PE5 || s == S_L5) ? 5
-       : s == S_L4 ? 4 : s == S_L3 ? 3 : s == S_L2 ? 2 : s == S_L1 ? 1 : 0;
-}
-__host__ __device__ constexpr int step_col0(int s) { return s == S_L5 ? 63 : 0; }
-__host__ __device__ constexpr int step_ncols(int s) { return (s == S_PE5 || s == S_P0) ? 63 : 256; }
-// trunk layer whose ReLU bit mask the step's epilogue applies (-1: none) and gradient-arena slot it writes
-__host__ __device__ constexpr int step_mask_layer(int s) {
-  return s == S_F ? 7 : s == S_L7 ? 6 : s == S_L6 ? 5 : s == S_L5 ? 4 : s == S_L4 ? 3 : s == S_L3 ? 2 : s == S_L2 ? 1
-       : s == S_L1 ? 0 : -1;
-}
-__host__ __device__ constexpr int step_out_slot(int s) {
-  return s == S_V1 ? arena::kGradFeat : s == S_F ? arena::kGradZ + 28 : s == S_L7 ? arena::kGradZ + 24
-       : s == S_L6 ? arena::kGradZ + 20 : s == S_L5 ? arena::kGradZ + 16 : s == S_L4 ? arena::kGradZ + 12
-       : s == S_L3 ? arena::kGradZ + 8 : s == S_L2 ? arena::kGradZ + 4 : s == S_L1 ? arena::kGradZ + 0 : -1;
-}
 
 // shared memory map
 constexpr uint32_t kOffA = 0, kOffW = 131072;
@@ -73,47 +38,6 @@ struct Bars {
 static_assert(sizeof(Bars) <= 256, "barrier block");
 
 }  // namespace bw
-
-size_t tc_bwd_wpack_bytes() { return (size_t)2 * bw::kNumStages * bw::kStageImage; }
-
-// Transposed weight stage images for the dgrad chain: stage (step s, k-block kb) = B[n][k] = W_layer[kb*64 + k][col0 + n]
-// for n < ncols (zero beyond), [N rows x 64 k] bf16, K-major, 128B swizzle.
-__global__ void pack_dgrad_weights_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack) {
-  using namespace bw;
-  const int64_t total = (int64_t)2 * kNumStages * 256 * 8;     // one thread per 16-byte chunk: (net, stage, n, 8 consecutive k)
-  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    // n fastest: neighbouring threads read neighbouring columns of the same weight rows
-    const int n = (int)(e & 255), kc = (int)((e >> 8) & 7);
-    const int stg = (int)((e >> 11) % kNumStages), net = (int)((e >> 11) / kNumStages);
-    int s = 0;
-    while (s + 1 < kNumSteps && step_stage0(s + 1) <= stg) ++s;
-    const int kb = stg - step_stage0(s);
-    if (n >= step_n(s)) continue;
-    const int layer = step_layer(s);
-    const LayerDim d = layer_dim(layer);
-    const bool col_ok = n < step_ncols(s);
-    const float* wcol = flat + (int64_t)net * NERF_PARAMS_PER_NET + w_off(layer) + step_col0(s) + n;
-    uint32_t pk[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float w2[2];
-#pragma unroll
-      for (int h2 = 0; h2 < 2; ++h2) {
-        const int out = kb * 64 + kc * 8 + 2 * j + h2;     // output feature of the layer = reduction index of dgrad
-        w2[h2] = (col_ok && out < d.out) ? __ldg(wcol + (int64_t)out * d.in) : 0.f;
-      }
-      const __nv_bfloat162 b2 = __floats2bfloat162_rn(w2[0], w2[1]);
-      pk[j] = *reinterpret_cast<const uint32_t*>(&b2);
-    }
-    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + stg) * kStageImage + sw128_offset(n, kc);
-    *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-  }
-}
-
-void tc_pack_dgrad_weights(NerfEngine* h, const float* flat, __nv_bfloat16* wpack, cudaStream_t st) {
-  pack_dgrad_weights_kernel<<<h->num_sms * 4, 256, 0, st>>>(flat, wpack);
-  h->launches++;
-}
 
 namespace bw {
 

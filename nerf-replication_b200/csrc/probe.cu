@@ -1,7 +1,7 @@
 // probe.cu -- bring-up battery for the hand-written tcgen05 path: one CTA, one 128 x N x K bf16 GEMM,
 // operands staged through shared memory (or TMEM for A) in each layout the engine uses.  Lets a GPU run
 // tell descriptor/layout bugs apart from pipeline bugs in the fused kernels.
-//   variant 0: A,B in smem, K-major, 128B swizzle        (layout of mlp_tc.cu)
+//   variant 0: A,B in smem, K-major, 128B swizzle        (the K-major operands of mlp_tc2.cu)
 //   variant 1: A,B in smem, K-major, no swizzle ("interleaved" 8x16B core matrices)
 //   variant 2: A in TMEM (bf16 pairs per 32-bit column), B in smem 128B swizzle
 #include "engine.h"

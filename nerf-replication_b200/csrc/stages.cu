@@ -484,6 +484,100 @@ void launch_mse_grad(NerfEngine* h, const float* rgb, const float* gt, int64_t n
 // ------------------------------------------------------------------------------------------------
 // composite backward (autograd of volume_renderer.py:67-96,414-430), one warp per ray.
 // Per-warp shared memory: T[S] | alpha[S] | ddelta[S].
+// composite_fwd_pass: T_i, alpha_i into shared memory (forward order); with `maps` it also folds the forward reductions
+// rgb / depth / acc in exactly the order composite_kernel uses (so a fused caller produces the same map bits).
+struct RayMaps { float r, g, b, depth, acc; };
+__device__ __forceinline__ RayMaps composite_fwd_pass(const float4* __restrict__ rr, const float* __restrict__ tt, int S, int lane,
+                                                      float* sT, float* sA, bool maps) {
+  const int nblk = (S + 31) / 32;
+  float carry = 1.0f, sr = 0.f, sg = 0.f, sb = 0.f, sd = 0.f, sa = 0.f;
+  for (int j = 0; j < nblk; ++j) {
+    const int i = j * 32 + lane;
+    const bool valid = i < S;
+    const float4 v = valid ? __ldg(rr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float sigma = fmaxf(v.w, 0.f);
+    const float ti = valid ? __ldg(tt + i) : 0.f;
+    const float tn = (i + 1 < S) ? __ldg(tt + i + 1) : 0.f;
+    AlphaQ a = alpha_q(sigma, ti, tn, i == S - 1);
+    const float q = valid ? a.q : 1.0f;
+    const float incl = warp_scan_mul(q, lane);
+    float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane == 0) excl = 1.0f;
+    const float T = carry * excl;
+    if (valid) { sT[i] = T; sA[i] = a.alpha; }
+    carry *= __shfl_sync(0xffffffffu, incl, 31);
+    if (maps) {
+      const float w = valid ? T * a.alpha : 0.f;
+      sr += w * sigmoid_fast(v.x); sg += w * sigmoid_fast(v.y); sb += w * sigmoid_fast(v.z);
+      sd += w * ti; sa += w;
+    }
+  }
+  RayMaps m{0.f, 0.f, 0.f, 0.f, 0.f};
+  if (maps) { m.r = warp_sum(sr); m.g = warp_sum(sg); m.b = warp_sum(sb); m.depth = warp_sum(sd); m.acc = warp_sum(sa); }
+  __syncwarp();
+  return m;
+}
+
+// Reverse pass of one ray: (d rgb_map = g0..g2, d depth_map = gd, direct d w from d_w_in -- a shared- or global-memory row
+// written earlier by this warp or by an earlier kernel; plain loads) -> d_raw row, d_t row (may be NULL).
+__device__ __forceinline__ void composite_bwd_ray(const float4* __restrict__ rr, const float* __restrict__ tt, int S, int white, int lane,
+                                                  float g0, float g1, float g2, float gd, const float* d_w_in,
+                                                  float4* __restrict__ d_raw_row, float* __restrict__ d_t_row,
+                                                  const float* sT, const float* sA, float* sD) {
+  const int nblk = (S + 31) / 32;
+  const float wb = white ? 1.0f : 0.0f;
+  // suffix sums S_k = sum_{j>k} dw_j w_j
+  float suffix_carry = 0.f;
+  for (int j = nblk - 1; j >= 0; --j) {
+    const int i = j * 32 + lane;
+    const bool valid = i < S;
+    float4 v = valid ? __ldg(rr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float T = valid ? sT[i] : 0.f, alpha = valid ? sA[i] : 0.f;
+    const float w = T * alpha;
+    const float c0 = sigmoid_cr(v.x), c1 = sigmoid_cr(v.y), c2 = sigmoid_cr(v.z);
+    float dw = g0 * (c0 - wb) + g1 * (c1 - wb) + g2 * (c2 - wb) + gd * (valid ? __ldg(tt + i) : 0.f);
+    if (d_w_in && valid) dw += d_w_in[i];
+    // inclusive suffix scan of dw*w over the lanes of this block
+    float sfx = valid ? dw * w : 0.f;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float nv = __shfl_down_sync(0xffffffffu, sfx, o);
+      if (lane + o < 32) sfx += nv;
+    }
+    const float own = valid ? dw * w : 0.f;
+    const float Sk = suffix_carry + (sfx - own);            // strictly-after sum
+    suffix_carry += __shfl_sync(0xffffffffu, sfx, 0);
+    if (valid) {
+      const float one_m_a = __fsub_rn(1.0f, alpha);
+      const float q = fminf(fmaxf(one_m_a, 1e-10f), 1.0f);
+      const float pass = (one_m_a >= 1e-10f && one_m_a <= 1.0f) ? 1.0f : 0.0f;   // clamp backward (inclusive)
+      const float dalpha = T * dw - pass * Sk / q;
+      const float sigma = fmaxf(v.w, 0.f);
+      const float ti = __ldg(tt + i);
+      const float delta = (i == S - 1) ? 1e10f : __fsub_rn(__ldg(tt + i + 1), ti);
+      const float e = exp_cr(-__fmul_rn(sigma, delta));      // d alpha / d x = exp(-x)
+      const float dx = dalpha * e;
+      const float dsigma = dx * delta;
+      sD[i] = (i == S - 1) ? 0.f : dx * sigma;               // d delta (last delta is a constant)
+      float4 o;
+      o.x = g0 * w * c0 * (1.0f - c0);
+      o.y = g1 * w * c1 * (1.0f - c1);
+      o.z = g2 * w * c2 * (1.0f - c2);
+      o.w = v.w > 0.f ? dsigma : 0.f;                        // relu backward
+      d_raw_row[i] = o;
+    }
+  }
+  __syncwarp();
+  if (d_t_row) {
+    for (int i = lane; i < S; i += 32) {
+      const float prev = i > 0 ? sD[i - 1] : 0.f;
+      // delta_{i-1} = t_i - t_{i-1}; delta_i = t_{i+1} - t_i; depth_map = sum w t adds gd * w_i
+      d_t_row[i] = prev - sD[i] + gd * sT[i] * sA[i];
+    }
+  }
+  __syncwarp();
+}
+
 __global__ void composite_bwd_kernel(const float4* __restrict__ raw, const float* __restrict__ t, int64_t n, int S,
                                      int white, const float* __restrict__ d_rgb_map, const float* __restrict__ d_depth_map,
                                      const float* __restrict__ d_w_in, float4* __restrict__ d_raw, float* __restrict__ d_t) {
@@ -492,81 +586,15 @@ __global__ void composite_bwd_kernel(const float4* __restrict__ raw, const float
   float* sT = smem + (size_t)warp * 3 * S;
   float* sA = sT + S;
   float* sD = sA + S;
-  const int nblk = (S + 31) / 32;
   for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerBlock + warp; ray < n; ray += (int64_t)gridDim.x * kWarpsPerBlock) {
     const float4* rr = raw + ray * S;
     const float* tt = t + ray * S;
-    // pass 1 (forward order): T_i, alpha_i
-    float carry = 1.0f;
-    for (int j = 0; j < nblk; ++j) {
-      const int i = j * 32 + lane;
-      const bool valid = i < S;
-      const float sigma = valid ? fmaxf(__ldg(rr + i).w, 0.f) : 0.f;
-      const float ti = valid ? __ldg(tt + i) : 0.f;
-      const float tn = (i + 1 < S) ? __ldg(tt + i + 1) : 0.f;
-      AlphaQ a = alpha_q(sigma, ti, tn, i == S - 1);
-      const float q = valid ? a.q : 1.0f;
-      const float incl = warp_scan_mul(q, lane);
-      float excl = __shfl_up_sync(0xffffffffu, incl, 1);
-      if (lane == 0) excl = 1.0f;
-      if (valid) { sT[i] = carry * excl; sA[i] = a.alpha; }
-      carry *= __shfl_sync(0xffffffffu, incl, 31);
-    }
-    __syncwarp();
+    composite_fwd_pass(rr, tt, S, lane, sT, sA, false);
     float g0 = 0.f, g1 = 0.f, g2 = 0.f;
     if (d_rgb_map) { g0 = __ldg(d_rgb_map + ray * 3); g1 = __ldg(d_rgb_map + ray * 3 + 1); g2 = __ldg(d_rgb_map + ray * 3 + 2); }
     const float gd = d_depth_map ? __ldg(d_depth_map + ray) : 0.f;
-    const float wb = white ? 1.0f : 0.0f;
-    // pass 2 (reverse order): suffix sums S_k = sum_{j>k} dw_j w_j
-    float suffix_carry = 0.f;
-    for (int j = nblk - 1; j >= 0; --j) {
-      const int i = j * 32 + lane;
-      const bool valid = i < S;
-      float4 v = valid ? __ldg(rr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-      const float T = valid ? sT[i] : 0.f, alpha = valid ? sA[i] : 0.f;
-      const float w = T * alpha;
-      const float c0 = sigmoid_cr(v.x), c1 = sigmoid_cr(v.y), c2 = sigmoid_cr(v.z);
-      float dw = g0 * (c0 - wb) + g1 * (c1 - wb) + g2 * (c2 - wb) + gd * (valid ? __ldg(tt + i) : 0.f);
-      if (d_w_in && valid) dw += __ldg(d_w_in + ray * S + i);
-      // inclusive suffix scan of dw*w over the lanes of this block
-      float sfx = valid ? dw * w : 0.f;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const float nv = __shfl_down_sync(0xffffffffu, sfx, o);
-        if (lane + o < 32) sfx += nv;
-      }
-      const float own = valid ? dw * w : 0.f;
-      const float Sk = suffix_carry + (sfx - own);            // strictly-after sum
-      suffix_carry += __shfl_sync(0xffffffffu, sfx, 0);
-      if (valid) {
-        const float one_m_a = __fsub_rn(1.0f, alpha);
-        const float q = fminf(fmaxf(one_m_a, 1e-10f), 1.0f);
-        const float pass = (one_m_a >= 1e-10f && one_m_a <= 1.0f) ? 1.0f : 0.0f;   // clamp backward (inclusive)
-        const float dalpha = T * dw - pass * Sk / q;
-        const float sigma = fmaxf(v.w, 0.f);
-        const float ti = __ldg(tt + i);
-        const float delta = (i == S - 1) ? 1e10f : __fsub_rn(__ldg(tt + i + 1), ti);
-        const float e = exp_cr(-__fmul_rn(sigma, delta));      // d alpha / d x = exp(-x)
-        const float dx = dalpha * e;
-        const float dsigma = dx * delta;
-        sD[i] = (i == S - 1) ? 0.f : dx * sigma;               // d delta (last delta is a constant)
-        float4 o;
-        o.x = g0 * w * c0 * (1.0f - c0);
-        o.y = g1 * w * c1 * (1.0f - c1);
-        o.z = g2 * w * c2 * (1.0f - c2);
-        o.w = v.w > 0.f ? dsigma : 0.f;                        // relu backward
-        d_raw[ray * S + i] = o;
-      }
-    }
-    __syncwarp();
-    if (d_t) {
-      for (int i = lane; i < S; i += 32) {
-        const float prev = i > 0 ? sD[i - 1] : 0.f;
-        // delta_{i-1} = t_i - t_{i-1}; delta_i = t_{i+1} - t_i; depth_map = sum w t adds gd * w_i
-        d_t[ray * S + i] = prev - sD[i] + gd * sT[i] * sA[i];
-      }
-    }
-    __syncwarp();
+    composite_bwd_ray(rr, tt, S, white, lane, g0, g1, g2, gd, d_w_in ? d_w_in + ray * S : nullptr, d_raw + ray * S,
+                      d_t ? d_t + ray * S : nullptr, sT, sA, sD);
   }
 }
 
@@ -581,16 +609,81 @@ void launch_composite_bwd(NerfEngine* h, const float* raw, const float* t, int64
   h->launches++;
 }
 
+// Fused tail of the training forward + head of the backward (one launch instead of composite + mse_grad + composite_bwd):
+// per ray  rgb_map = composite(raw, t)  (volume_renderer.py:414-430; same arithmetic and reduction order as composite_kernel),
+// err = rgb_map - gt, d rgb_map = 2 err / (3 n) * scale (MSELoss, trainers/nerf.py:33), then the composite backward.
+// Loss: every warp leaves its ray's squared error in sq[ray]; the last block to finish folds sq[0..n) in a fixed order
+// (deterministic, like the one-block mse_grad_kernel) and resets the counter.
+__global__ void composite_loss_bwd_kernel(const float4* __restrict__ raw, const float* __restrict__ t, int64_t n, int S, int white,
+                                          const float* __restrict__ gt, float gscale, float* __restrict__ rgb_out,
+                                          float4* __restrict__ d_raw, float* __restrict__ d_t, float* __restrict__ sq,
+                                          unsigned int* __restrict__ done, float* __restrict__ loss) {
+  extern __shared__ float smem[];
+  __shared__ float red[kWarpsPerBlock];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* sT = smem + (size_t)warp * 3 * S;
+  float* sA = sT + S;
+  float* sD = sA + S;
+  for (int64_t ray = blockIdx.x * (int64_t)kWarpsPerBlock + warp; ray < n; ray += (int64_t)gridDim.x * kWarpsPerBlock) {
+    const float4* rr = raw + ray * S;
+    const float* tt = t + ray * S;
+    RayMaps m = composite_fwd_pass(rr, tt, S, lane, sT, sA, true);
+    if (white) { const float bg = 1.0f - m.acc; m.r += bg; m.g += bg; m.b += bg; }
+    const float e0 = m.r - __ldg(gt + ray * 3), e1 = m.g - __ldg(gt + ray * 3 + 1), e2 = m.b - __ldg(gt + ray * 3 + 2);
+    if (lane == 0) {
+      if (rgb_out) { rgb_out[ray * 3] = m.r; rgb_out[ray * 3 + 1] = m.g; rgb_out[ray * 3 + 2] = m.b; }
+      sq[ray] = (e0 * e0 + e1 * e1) + e2 * e2;
+    }
+    composite_bwd_ray(rr, tt, S, white, lane, e0 * gscale, e1 * gscale, e2 * gscale, 0.f, nullptr, d_raw + ray * S,
+                      d_t ? d_t + ray * S : nullptr, sT, sA, sD);
+  }
+  // last block: deterministic fold of the per-ray squared errors
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  float acc = 0.f;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += __ldcg(sq + i);
+  acc = warp_sum(acc);
+  if (lane == 0) red[warp] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = 0.f;
+    for (int w = 0; w < kWarpsPerBlock; ++w) v += red[w];
+    *loss = v / (3.0f * (float)n);
+    *done = 0u;
+  }
+}
+
+void launch_composite_loss_bwd(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white, const float* gt,
+                               float scale, float* rgb_out, float* d_raw, float* d_t, float* sq, unsigned int* done, float* loss,
+                               cudaStream_t st) {
+  if (n <= 0) return;
+  const size_t smem = (size_t)kWarpsPerBlock * 3 * S * sizeof(float);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(composite_loss_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const float gscale = 2.0f * scale / (3.0f * (float)n);
+  composite_loss_bwd_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
+      reinterpret_cast<const float4*>(raw), t, n, S, white, gt, gscale, rgb_out, reinterpret_cast<float4*>(d_raw), d_t, sq, done, loss);
+  h->launches++;
+}
+
 // ------------------------------------------------------------------------------------------------
 // sample_pdf backward: d t_sorted -> (un-sort) d t_fine -> d cdf (scatter) -> d pdf (suffix sum) ->
 // d w_coarse.  Forward quantities are recomputed.  Per-warp smem: forward layout + dcdf[Nc] + dtf[Nf].
+// d_raw_c != NULL (fused training step): the coarse composite backward runs in the same warp on the d w row it has just
+// produced (kept in shared memory; + 3 Nc floats of T / alpha / d delta) and writes d_raw_c [n,Nc,4] -- d_w_coarse may
+// then be NULL.  Only d sigma is non-zero there: the coarse maps are not in the loss.
 __global__ void sample_pdf_bwd_kernel(const float4* __restrict__ raw_c, const float* __restrict__ t_c, int64_t n, int Nc,
                                       int Nf, int Npad, const float* __restrict__ u, int philox, uint64_t seed,
                                       uint64_t call_id, const float* __restrict__ d_t_sorted,
-                                      const int32_t* __restrict__ sort_idx, float* __restrict__ d_w_coarse) {
+                                      const int32_t* __restrict__ sort_idx, float* __restrict__ d_w_coarse,
+                                      int white, float4* __restrict__ d_raw_c) {
   extern __shared__ float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int per_warp = 2 * Nc + 2 * Npad + Nc + Nf;
+  const int per_warp = 2 * Nc + 2 * Npad + Nc + Nf + (d_raw_c ? 3 * Nc : 0);
   float* base = smem + (size_t)warp * per_warp;
   PdfSmem s; s.tc = base; s.cdf = base + Nc; s.keys = base + 2 * Nc; s.kidx = reinterpret_cast<int*>(base + 2 * Nc + Npad);
   float* dcdf = base + 2 * Nc + 2 * Npad;
@@ -648,22 +741,29 @@ __global__ void sample_pdf_bwd_kernel(const float4* __restrict__ raw_c, const fl
     for (int i = lane; i < Nc; i += 32) {
       float o = 0.f;
       if (i >= 1 && i <= Nc - 2) o = (dcdf[i] - dot) / ssum;   // dcdf[i] holds dpdf_{i-1}
-      d_w_coarse[ray * Nc + i] = o;
+      if (d_w_coarse) d_w_coarse[ray * Nc + i] = o;
+      if (d_raw_c) dcdf[i] = o;                                // same index read above: in place
     }
     __syncwarp();
+    if (d_raw_c) {
+      float* sT = dtf + Nf;
+      composite_fwd_pass(raw_c + ray * Nc, t_c + ray * Nc, Nc, lane, sT, sT + Nc, false);
+      composite_bwd_ray(raw_c + ray * Nc, t_c + ray * Nc, Nc, white, lane, 0.f, 0.f, 0.f, 0.f, dcdf, d_raw_c + ray * Nc, nullptr,
+                        sT, sT + Nc, sT + 2 * Nc);
+    }
   }
 }
 
 int launch_sample_pdf_bwd(NerfEngine* h, const float* raw_c, const float* t_c, int64_t n, int Nc, int Nf,
                           const float* u, bool philox_u, uint64_t call_id, const float* d_t_sorted,
-                          const int32_t* sort_idx, float* d_w_coarse, cudaStream_t st) {
+                          const int32_t* sort_idx, float* d_w_coarse, cudaStream_t st, int white, float* d_raw_c) {
   if (n <= 0) return NERF_OK;
   const int Npad = next_pow2(Nc + Nf);
-  const size_t smem = (size_t)kWarpsPerBlock * (2 * Nc + 2 * Npad + Nc + Nf) * sizeof(float);
+  const size_t smem = (size_t)kWarpsPerBlock * (2 * Nc + 2 * Npad + Nc + Nf + (d_raw_c ? 3 * Nc : 0)) * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(sample_pdf_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   sample_pdf_bwd_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw_c), t_c, n, Nc, Nf, Npad, u, philox_u ? 1 : 0, h->cfg.seed, call_id,
-      d_t_sorted, sort_idx, d_w_coarse);
+      d_t_sorted, sort_idx, d_w_coarse, white, reinterpret_cast<float4*>(d_raw_c));
   h->launches++;
   return NERF_OK;
 }

@@ -236,9 +236,11 @@ class Engine:
         return rgb, depth
 
     # -- training -------------------------------------------------------------------------------
-    def forward_backward(self, rays_o, rays_d, rgb_gt, flat_grad, jitter=None, u=None, grad_scale=1.0, want_rgb=False):
+    def forward_backward(self, rays_o, rays_d, rgb_gt, flat_grad, jitter=None, u=None, grad_scale=1.0, want_rgb=False, loss=None):
+        """One fused step body: flat_grad = grad_scale * d MSE / d params (overwritten), -> loss (device scalar).  Passing the
+        same ``loss`` / ``flat_grad`` tensors (and n) on every call lets the engine replay the step as one CUDA graph."""
         n = rays_o.shape[0]
-        loss = torch.empty((), device=rays_o.device)
+        loss = torch.empty((), device=rays_o.device) if loss is None else loss
         rgb = torch.empty(n, 3, device=rays_o.device) if want_rgb else None
         self._check(self.lib.nerf_forward_backward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"),
                                                    self._p(rgb_gt, name="rgb_gt"), n, self._p(jitter, name="jitter"),
@@ -248,18 +250,28 @@ class Engine:
         return (loss, rgb) if want_rgb else loss
 
     def train_forward(self, rays_o, rays_d, jitter=None, u=None):
+        """-> (rgb, depth, forward_id); the handle keeps this forward's activations until its train_backward."""
         n = rays_o.shape[0]
         rgb, depth = torch.empty(n, 3, device=rays_o.device), torch.empty(n, device=rays_o.device)
+        fid = C.c_uint64(0)
         self._check(self.lib.nerf_train_forward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"), n,
                                                 self._p(jitter, name="jitter"), self._p(u, name="u"), rgb.data_ptr(),
-                                                depth.data_ptr(), self._stream()))
-        return rgb, depth
+                                                depth.data_ptr(), C.byref(fid), self._stream()))
+        return rgb, depth, fid.value
 
-    def train_backward(self, rays_o, rays_d, d_rgb, d_depth, flat_grad, zero_grad=True):
+    def train_backward(self, rays_o, rays_d, d_rgb, d_depth, flat_grad, zero_grad=True, forward_id=0):
+        """forward_id (from train_forward): raises if a later forward has overwritten that forward's activations."""
         n = rays_o.shape[0]
         self._check(self.lib.nerf_train_backward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"), n,
                                                  self._p(d_rgb, name="d_rgb"), self._p(d_depth, name="d_depth"),
-                                                 self._p(flat_grad, name="flat_grad"), int(zero_grad), self._stream()))
+                                                 self._p(flat_grad, name="flat_grad"), int(zero_grad), int(forward_id), self._stream()))
+
+    def stream_wait_fine_grads(self, stream):
+        """Makes `stream` (a torch.cuda.Stream) wait until the fine net's half of the last backward's flat_grad is final."""
+        self._check(self.lib.nerf_stream_wait_fine_grads(self.h, C.c_void_p(stream.cuda_stream)))
+
+    def set_graph_mode(self, on=True):
+        self._check(self.lib.nerf_set_graph_mode(self.h, int(bool(on))))
 
     def clip_adam(self, flat_param, flat_grad, m, v, step, lr=5e-4, beta1=0.9, beta2=0.999, eps=1e-8, clip=40.0):
         self._check(self.lib.nerf_clip_adam(self.h, self._p(flat_param, name="flat_param"), self._p(flat_grad, name="flat_grad"),
@@ -343,7 +355,7 @@ class Engine:
             M, K = a.shape
             N = b.shape[0]
         d = torch.zeros(M, N, device=a.device)
-        rc = self.lib.nerf_debug_umma_probe(variant, self._p(a, name="a"), self._p(b, name="b"), d.data_ptr(), M, N, K, self._stream())
+        rc = L.load_probe().nerf_debug_umma_probe(variant, self._p(a, name="a"), self._p(b, name="b"), d.data_ptr(), M, N, K, self._stream())
         if rc != 0:
             raise EngineError("umma probe launch failed (%d)" % rc)
         return d

@@ -4,7 +4,9 @@
 pass.  Under ``torch.no_grad()`` it is one call into the fused CUDA pipeline; with gradients enabled it goes
 through a ``torch.autograd.Function`` whose backward runs the engine's hand-written backward kernels and
 hands each ``nn.Parameter`` its gradient, so the reference's ``loss.backward(); clip_grad_value_; optimizer.step``
-lines (trainer.py:56-60) work unchanged.  ``render(batch, return_dict=True)`` (or ``cfg.return_dict``) is the
+lines (trainer.py:56-60) work unchanged.  Restriction: the engine keeps the activations of ONE grad-enabled render, so
+each such render must be followed by its own backward before the next one (two renders, then one backward over both,
+raises).  ``render(batch, return_dict=True)`` (or ``cfg.return_dict``) is the
 opt-in extension that also returns acc and the coarse maps.
 """
 import torch
@@ -17,7 +19,7 @@ class _RenderFn(torch.autograd.Function):
     def forward(ctx, renderer, rays_o, rays_d, jitter, u, *params):
         net = renderer.net
         eng = renderer._engine()
-        rgb, depth = eng.train_forward(rays_o, rays_d, jitter, u)
+        rgb, depth, ctx.forward_id = eng.train_forward(rays_o, rays_d, jitter, u)
         ctx.renderer, ctx.rays = renderer, (rays_o, rays_d)
         return rgb, depth
 
@@ -29,7 +31,9 @@ class _RenderFn(torch.autograd.Function):
         scratch = torch.empty_like(net.flat_params)
         d_rgb = None if d_rgb is None else d_rgb.contiguous()
         d_depth = None if d_depth is None else d_depth.contiguous()
-        eng.train_backward(rays_o, rays_d, d_rgb, d_depth, scratch, zero_grad=True)
+        # one forward, then its backward: the engine keeps the activations of the latest grad-enabled render only and
+        # raises (instead of silently using another batch's activations) if a second render ran in between
+        eng.train_backward(rays_o, rays_d, d_rgb, d_depth, scratch, zero_grad=True, forward_id=ctx.forward_id)
         grads, o = [], 0
         for p in net.parameters():
             n = p.numel()

@@ -18,7 +18,8 @@ def shard_range(n, rank, world):
 
 
 def allreduce_mean_(flat_grad, world=None, group=None):
-    """DDP semantics: gradients are averaged over ranks.  No-op for a single process."""
+    """DDP semantics: gradients are averaged over ranks.  No-op for a single process.  (Stand-alone form: a separate
+    division after the sum.  The trainers below fold the 1/world into the backward's grad_scale and call GradReducer.)"""
     if not (dist.is_available() and dist.is_initialized()):
         return flat_grad
     world = dist.get_world_size(group) if world is None else world
@@ -28,23 +29,61 @@ def allreduce_mean_(flat_grad, world=None, group=None):
     return flat_grad
 
 
+def dist_world(group=None):
+    return dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+
+
+class GradReducer:
+    """The path's one collective: SUM all-reduce of the flat gradient whose 1/world factor is already inside it
+    (the backward ran with grad_scale = 1/world, so no division kernel follows) -- DDP's mean, trainer.py:16-21.
+
+    ``overlap`` (GPU / NCCL): the fine net's half of the buffer is final before the coarse net's backward starts
+    (``nerf_stream_wait_fine_grads``), so it is reduced on a side stream while ``sample_pdf_bwd`` and the coarse dgrad / wgrad
+    kernels run; the coarse half follows on the compute stream, which then joins the side stream before clip + Adam.
+    With ``overlap=False`` (and always on CPU tensors / gloo) the whole buffer is reduced in one call after the backward."""
+
+    def __init__(self, n_fine_offset, overlap=True, group=None):
+        self.split, self.overlap, self.group = int(n_fine_offset), bool(overlap), group
+        self._comm = None
+
+    def __call__(self, flat_grad, engine=None):
+        world = dist_world(self.group)
+        if world <= 1:
+            return flat_grad
+        if not (self.overlap and flat_grad.is_cuda and engine is not None):
+            dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+            return flat_grad
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=flat_grad.device)
+        cur = torch.cuda.current_stream(flat_grad.device)
+        engine.stream_wait_fine_grads(self._comm)                 # side stream: starts when the fine net's gradients are final
+        with torch.cuda.stream(self._comm):
+            dist.all_reduce(flat_grad[self.split:], op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(flat_grad[:self.split], op=dist.ReduceOp.SUM, group=self.group)     # after the whole backward
+        cur.wait_stream(self._comm)
+        return flat_grad
+
+
 def exponential_lr(base_lr, epoch, gamma=0.1, decay_epochs=500):
     """ExponentialLR of src/utils/optimizer/lr_scheduler.py:68-79 (stepped per epoch, train.py:66)."""
     return base_lr * gamma ** (epoch / decay_epochs)
 
 
 class FusedTrainer:
-    def __init__(self, net, cfg=None, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, clip=40.0):
+    def __init__(self, net, cfg=None, lr=5e-4, betas=(0.9, 0.999), eps=1e-8, clip=40.0, overlap=True):
         self.net = net
         self.renderer = Renderer(net, cfg)
         self.lr, self.betas, self.eps, self.clip = lr, betas, eps, clip
         flat = net.flat_params
         self.m, self.v = torch.zeros_like(flat), torch.zeros_like(flat)
         self.step_count = 0
+        self.reduce = GradReducer(flat.numel() // 2, overlap=overlap)
+        self._loss = torch.zeros((), device=flat.device)      # persistent: the step's CUDA graph writes the loss here
 
-    def forward_backward(self, rays_o, rays_d, rgb_gt, jitter=None, u=None):
+    def forward_backward(self, rays_o, rays_d, rgb_gt, jitter=None, u=None, grad_scale=None):
         eng = self.renderer._engine()
-        return eng.forward_backward(rays_o, rays_d, rgb_gt, self.net.flat_grad, jitter=jitter, u=u)
+        scale = 1.0 / dist_world() if grad_scale is None else grad_scale
+        return eng.forward_backward(rays_o, rays_d, rgb_gt, self.net.flat_grad, jitter=jitter, u=u, grad_scale=scale, loss=self._loss)
 
     def apply(self):
         eng = self.renderer._engine()
@@ -54,8 +93,9 @@ class FusedTrainer:
         self.net.mark_packed()
 
     def step(self, rays_o, rays_d, rgb_gt, jitter=None, u=None):
+        """-> this rank's loss (device scalar, overwritten by the next step)."""
         loss = self.forward_backward(rays_o, rays_d, rgb_gt, jitter, u)
-        allreduce_mean_(self.net.flat_grad)
+        self.reduce(self.net.flat_grad, self.renderer._engine())
         self.apply()
         return loss
 
@@ -198,6 +238,15 @@ class Trainer:
         self.renderer = self.wrapper.renderer
         self.log_interval = getattr(cfg, "log_interval", log_interval) if cfg is not None else log_interval
         self.clip, self.local_rank, self.global_step, self.verbose = clip, rank, 0, verbose
+        self._loss, self.reduce = None, None
+
+    def _clip_unfused(self, optimizer):
+        """trainer.py:59 clip_grad_value_(params, 40).  FusedAdam clips inside its kernel (``optimizer.clip``); for any other
+        optimizer (e.g. the torch.optim.Adam the reference's make_optimizer builds) the flat gradient is clamped here, so
+        the clip is never silently dropped.  torch.clamp keeps NaN, like clip_grad_value_."""
+        from .optimizer import FusedAdam
+        if not isinstance(optimizer, FusedAdam) and self.clip:
+            self.net.flat_grad.clamp_(-self.clip, self.clip)
 
     def train(self, epoch, data_loader, optimizer, recorder, jitter=None, u=None):
         ds = data_loader.dataset
@@ -205,25 +254,31 @@ class Trainer:
         optimizer.clip = self.clip                      # clip_grad_value_(…, 40) fused into the Adam kernel (trainer.py:59)
         max_iter, end = len(data_loader), time.time()
         losses = torch.zeros(max_iter, device=self.net.flat_params.device)
+        world = dist_world()
+        if self._loss is None:
+            self._loss = torch.zeros((), device=self.net.flat_params.device)
+            self.reduce = GradReducer(self.net.flat_params.numel() // 2)
         for iteration, (view, draw) in enumerate(data_loader):
             data_time = time.time() - end
             eng = self.renderer._engine()
             if eng.cfg.seed != ds.seed:
                 eng.configure(seed=ds.seed)             # the pixel draw is keyed by (dataset seed, draw)
             eng.bank_train_step(ds.bank, view, ds.n_rays, self.net.flat_grad, mode="random", draw=draw, jitter=jitter, u=u,
-                                loss=losses[iteration])
-            allreduce_mean_(self.net.flat_grad)
+                                grad_scale=1.0 / world, loss=self._loss)
+            losses[iteration].copy_(self._loss)         # the step (a replayed CUDA graph) always writes the same scalar
+            self.reduce(self.net.flat_grad, eng)
+            self._clip_unfused(optimizer)
             optimizer.step()
             iteration += 1
             if self.local_rank > 0:
                 continue
             recorder.step += 1
             self.global_step += 1
+            recorder.batch_time.update(time.time() - end)   # every iteration (launch-side time; the GPU runs at most one loss read behind)
+            recorder.data_time.update(data_time)
             if iteration % self.log_interval == 0 or iteration == max_iter - 1:
                 loss = float(losses[iteration - 1])     # the only device->host read of the loop
                 recorder.update_loss_stats({"loss": loss, "psnr": -10.0 * math.log10(max(loss, 1e-30))})
-                recorder.batch_time.update(time.time() - end)
-                recorder.data_time.update(data_time)
                 if self.verbose:
                     eta = str(datetime.timedelta(seconds=int(recorder.batch_time.global_avg * (max_iter - iteration))))
                     print("  ".join(["eta: %s" % eta, str(recorder), "lr: %.6f" % optimizer.param_groups[0]["lr"],

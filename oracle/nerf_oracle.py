@@ -10,6 +10,12 @@ tree exists) executes the unmodified reference (``oracle/ref_loader.py``) and ch
 this restatement against it bit-for-bit on CPU, then writes ``tests/golden/*.npz``;
 ``tests/test_oracle.py`` re-checks this file against those goldens everywhere.
 
+Every tensor is created on the device of its inputs, so the same restatement also runs on a GPU (weights and rays moved
+there by the caller): ``bench.py``'s ``gpu_baseline`` times it on the B200 as the like-for-like "before" figure -- eager
+PyTorch, fp32 (TF32 off), MLP chunks of 512 rows, fine pass in sample blocks of 64, exactly the reference's launch structure
+(volume_renderer.py:382-405, network.py:163-171) -- and the parity tests use it as a fast fp32 oracle for whole views after
+checking it against this file's CPU results.
+
 Citations are ``file:line`` relative to the reference root.
 """
 import math
@@ -108,8 +114,8 @@ def get_rays_np(c2w, H, W, pixel_ids=None, camera_angle_x=CAMERA_ANGLE_X):
 
 # ----------------------------------------------------------------------------------------------
 # a-C  stratified sampling (volume_renderer.py:27-65)
-def stratified_t(n_rays, n_samples, jitter=None, near=NEAR, far=FAR):
-    t_lin = torch.linspace(near, far, n_samples)                   # :44
+def stratified_t(n_rays, n_samples, jitter=None, near=NEAR, far=FAR, device=None):
+    t_lin = torch.linspace(near, far, n_samples, device=device)    # :44
     t = t_lin.unsqueeze(0).expand(n_rays, n_samples).clone()       # :45
     if jitter is not None:                                         # perturb, :48-60
         mids = 0.5 * (t_lin[1:] + t_lin[:-1])
@@ -127,7 +133,7 @@ def points_on_rays(rays_o, rays_d, t):
 # a-D  frequency encoding (src/models/encoding/freq.py:7-32, encoding/__init__.py:6-18)
 def freq_encode(x, n_freqs):
     outs = [x]
-    for band in (2.0 ** torch.linspace(0.0, n_freqs - 1, steps=n_freqs)):
+    for band in (2.0 ** torch.linspace(0.0, n_freqs - 1, steps=n_freqs)).tolist():   # exact powers of two
         outs.append(torch.sin(x * band))
         outs.append(torch.cos(x * band))
     return torch.cat(outs, -1)
@@ -168,7 +174,7 @@ def network_forward(sd, pts, viewdirs, valid_mask=None, model="", chunk=512):
     flat = torch.cat(outs, 0) if outs else emb.new_zeros((0, 4))
     if valid_mask is None:
         return flat.reshape(R, S, 4)
-    out = torch.zeros(R * S, 4)
+    out = torch.zeros(R * S, 4, device=flat.device)
     out[m] = flat                                           # masked points -> raw = 0 (:235-253)
     return out.reshape(R, S, 4)
 
@@ -179,7 +185,7 @@ def weights_computation(sigma, t):
     delta = t[..., 1:] - t[..., :-1]
     delta = torch.cat([delta, 1e10 * torch.ones_like(delta[..., :1])], -1)       # :80-81
     alpha = 1.0 - torch.exp(-sigma * delta)                                      # :84
-    tmp = torch.cat([torch.ones(alpha.shape[0], 1), torch.clamp(1.0 - alpha, min=1e-10, max=1.0)], -1)
+    tmp = torch.cat([torch.ones(alpha.shape[0], 1, device=alpha.device), torch.clamp(1.0 - alpha, min=1e-10, max=1.0)], -1)
     T = torch.cumprod(tmp, -1)[:, :-1]                                           # :87-91
     return T, T * alpha                                                          # :94
 
@@ -197,7 +203,7 @@ def sample_pdf(sigma_c, t_c, n_importance, u=None, eps=1e-5, taps=None, fast_sam
     cdf = torch.cumsum(pdf, -1)
     cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)  # [N, Nc-1]
     if u is None:
-        u = torch.linspace(0.0, 1.0, steps=n_importance).expand(list(cdf.shape[:-1]) + [n_importance])
+        u = torch.linspace(0.0, 1.0, steps=n_importance, device=cdf.device).expand(list(cdf.shape[:-1]) + [n_importance])
     u = u.contiguous()
     inds = torch.searchsorted(cdf, u, right=True)               # :151
     below = torch.clamp(inds - 1, 0, n_samples - 3)             # :153  (the Nc-3 quirk, fact 7)
@@ -251,7 +257,7 @@ def render(sd, rays_o, rays_d, n_samples=64, n_importance=128, white_bkgd=True,
     """rays_o/rays_d [N,3] fp32 -> (rgb [N,3], depth [N]) of the final pass.  ``taps`` (dict)
     receives every intermediate; ``jitter``/``u`` inject the perturb / train-mode random numbers."""
     N = rays_o.shape[0]
-    t_c = stratified_t(N, n_samples, jitter)
+    t_c = stratified_t(N, n_samples, jitter, device=rays_o.device)
     pts_c = points_on_rays(rays_o, rays_d, t_c)
     viewdirs = rays_d / torch.norm(rays_d, dim=-1, keepdim=True)     # :314
     raw_c = network_forward(sd, pts_c, viewdirs, None, "", chunk)
@@ -270,7 +276,7 @@ def render(sd, rays_o, rays_d, n_samples=64, n_importance=128, white_bkgd=True,
         depth, idx = torch.sort(depth, dim=-1)                       # :353
         pts = torch.gather(torch.cat([pts_c, pts_f], 1), 1, idx.unsqueeze(-1).expand(-1, -1, 3))
         if fast_sampling:                                            # :359-370: coarse samples stay valid, same permutation
-            valid_sorted = torch.gather(torch.cat([torch.ones(N, n_samples, dtype=torch.bool), valid_f], 1), 1, idx)
+            valid_sorted = torch.gather(torch.cat([torch.ones(N, n_samples, dtype=torch.bool, device=valid_f.device), valid_f], 1), 1, idx)
             tp.update(valid_sorted=valid_sorted)
         raw = torch.cat([network_forward(sd, pts[:, j:j + 64], viewdirs,
                                          None if valid_sorted is None else valid_sorted[:, j:j + 64], "fine", chunk)

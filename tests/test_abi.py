@@ -39,10 +39,21 @@ def test_ctypes_signatures_cover_header(built_lib):
     assert lib.nerf_version() >= 100
 
 
+def test_probe_library_is_separate_from_the_product(built_lib):
+    """The bring-up probe battery has its own header and library; the product .so does not export it."""
+    from nerf_replication_b200 import _lib
+    probe_header = open(os.path.join(ROOT, "include", "nerf_b200_probe.h")).read()
+    probe_header = re.sub(r"/\*.*?\*/", "", probe_header, flags=re.S)
+    assert sorted(set(re.findall(r"\b(nerf_[a-z0-9_]+)\s*\(", probe_header))) == sorted(_lib.PROBE_SIGNATURES)
+    probe = _lib.load_probe()
+    assert hasattr(probe, "nerf_debug_umma_probe")
+    assert not hasattr(ctypes.CDLL(built_lib), "nerf_debug_umma_probe")
+
+
 def test_header_is_plain_c(tmp_path):
     """No torch / C++ types in the boundary: the header must compile as C."""
     c = tmp_path / "t.c"
-    c.write_text('#include "nerf_b200.h"\nint main(void){NerfConfig c; (void)c; return NERF_PARAMS_TOTAL == 2*NERF_PARAMS_PER_NET ? 0 : 1;}\n')
+    c.write_text('#include "nerf_b200.h"\n#include "nerf_b200_probe.h"\nint main(void){NerfConfig c; (void)c; return NERF_PARAMS_TOTAL == 2*NERF_PARAMS_PER_NET ? 0 : 1;}\n')
     exe = tmp_path / "t"
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)])
     assert subprocess.call([str(exe)]) == 0

@@ -11,7 +11,7 @@ import torch.multiprocessing as mp
 from nerf_replication_b200 import config as C
 from nerf_replication_b200.network import Network
 from nerf_replication_b200.renderer import Renderer
-from nerf_replication_b200.trainer import allreduce_mean_, exponential_lr, shard_range
+from nerf_replication_b200.trainer import GradReducer, allreduce_mean_, exponential_lr, shard_range
 
 
 def test_knob_precedence():
@@ -20,7 +20,10 @@ def test_knob_precedence():
     cfg.N_samples = 32
     assert C.knob(cfg, "N_samples", 7) == 32            # top-level wins (volume_renderer.py:14)
     assert C.knob(cfg, "weights_threshold", 0.25) == 0.25
-    assert C.knob({"task_arg": {"N_importance": 5}}, "N_importance", 128) == 5
+    # the task_arg fallback is an opt-in of the standalone cfg; a cfg without the flag (the reference's) is read like the
+    # reference reads it: top level or default (volume_renderer.py:14-24)
+    assert C.knob({"task_arg": {"N_importance": 5}, "renderer_task_arg_fallback": True}, "N_importance", 128) == 5
+    assert C.knob({"task_arg": {"N_importance": 5}}, "N_importance", 128) == 128
 
 
 def test_renderer_reads_reference_keys():
@@ -96,6 +99,39 @@ def _ddp_worker(rank, world, port, out):
     dist.all_reduce(t)
     out[world + rank] = int(t)
     dist.destroy_process_group()
+
+
+def _reducer_worker(rank, world, port, out):
+    """The trainers' data-parallel step in miniature: every rank's backward already carries 1/world (grad_scale), the
+    reducer sums; the result must be DDP's mean and identical on all ranks, and a clip + Adam step on it keeps replicas equal."""
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n = 1191688
+    gen = torch.Generator().manual_seed(100 + rank)
+    g_local = torch.randn(n, generator=gen)                       # this rank's unscaled gradient
+    g = g_local / world                                           # what nerf_forward_backward(grad_scale=1/world) leaves in flat_grad
+    GradReducer(n // 2, overlap=True)(g, engine=None)             # CPU tensors / gloo: one all-reduce of the whole buffer
+    p = torch.nn.Parameter(torch.zeros(n))
+    p.grad = g.clone()
+    torch.nn.utils.clip_grad_value_([p], 40.0)
+    opt = torch.optim.Adam([p], lr=5e-4, eps=1e-8)
+    opt.step()
+    out[rank] = (g[:4].clone(), g[n // 2:n // 2 + 4].clone(), float(p.detach().double().sum()), g_local[:4].clone(), g_local[n // 2:n // 2 + 4].clone())
+    dist.destroy_process_group()
+
+
+def test_grad_reducer_sums_prescaled_gradients_world2_gloo():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_reducer_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    mean_c = (out[0][3] + out[1][3]) / 2
+    mean_f = (out[0][4] + out[1][4]) / 2
+    for r in range(world):
+        torch.testing.assert_close(out[r][0], mean_c)
+        torch.testing.assert_close(out[r][1], mean_f)
+    assert out[0][2] == out[1][2]                                  # replicas stay bit-identical after the update
 
 
 def test_gradient_allreduce_world2_gloo():
