@@ -226,7 +226,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": metric_name(), "value": v, "unit": "rays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "config": workload_config(args, max(args.gpus, 1)),      # the same workload object as the GPU arm's line (one frame)
         "cpu_baseline": {"value": v, "unit": "rays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -410,45 +410,47 @@ def main():
 
     do_render = args.mode in ("all", "render")
     do_train = args.mode in ("all", "train") and args.fast_sampling is None
-    sampler = ClockSampler(physical_gpu_index(local_rank))
-    sampler.start()
-    eng.profile(True)
-    mark = {}
+    value = None
+    if do_render:
+        sampler = ClockSampler(physical_gpu_index(local_rank))
+        sampler.start()
+        eng.profile(True)
+        mark = {}
 
-    def reset_counters():
-        eng.profile_read()
-        mark["launches0"] = eng.launch_count
+        def reset_counters():
+            eng.profile_read()
+            mark["launches0"] = eng.launch_count
 
-    ms_dev = timed(render_step_device, args.steps, args.warmup, "events", after_warmup=reset_counters)
-    launches = eng.launch_count - mark["launches0"]
-    mlp_ms, mlp_launches, mlp_rows = eng.profile_read_classes()["fwd"]
-    eng.profile(False)
-    clocks = sampler.finish()
-    ms_e2e = timed(render_step_e2e, args.steps, args.warmup, "wall")
+        ms_dev = timed(render_step_device, args.steps, args.warmup, "events", after_warmup=reset_counters)
+        launches = eng.launch_count - mark["launches0"]
+        mlp_ms, mlp_launches, mlp_rows = eng.profile_read_classes()["fwd"]
+        eng.profile(False)
+        clocks = sampler.finish()
+        ms_e2e = timed(render_step_e2e, args.steps, args.warmup, "wall")
 
-    total_ms = sum(ms_dev)
-    value = H * W * args.steps / (total_ms / 1e3)
-    e2e_value = H * W * args.steps / (sum(ms_e2e) / 1e3)
-    flop_per_ray = (2 * N_SAMPLES + N_IMPORTANCE) * FLOP_PER_EVAL
-    roofline = None
-    if precision == "bf16" and mlp_launches > 0 and mlp_ms > 0 and args.fast_sampling is None:
-        # event brackets around every fused-MLP launch of the timed steps, on the launching stream
-        achieved = mlp_rows * FLOP_PER_EVAL / (mlp_ms / 1e3) / 1e12
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_sus, "unit": "TFLOP/s", "frac": achieved / peak_sus,
-                    "traffic": NCU_TRAFFIC_BYTES["render"]["fwd"], "traffic_unit": "bytes per launch (ncu dram read + write, fine-net launch)",
-                    "kernel": "mlp_tc2_forward_kernel (CTA pair, tcgen05 cta_group::2)",
-                    "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst),
-                    "launches_timed": mlp_launches, "avg_launch_ms": mlp_ms / mlp_launches,
-                    "share_of_step": mlp_ms / total_ms if world == 1 else None,
-                    "step_tflops_per_gpu": n_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12}
-    line.update({"value": value, "ms_per_step": total_ms / args.steps,
-                 "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": H * W * 24, "d2h_bytes_per_step": H * W * 16,
-                         "ms_per_step": sum(ms_e2e) / args.steps,
-                         "api": "nerf_render_rays_host (C ABI, host buffers)" if world == 1 else
-                                "pinned host rays -> H2D -> Renderer.render (band) -> NCCL all-gather -> D2H of the frame on rank 0"},
-                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline})
-    if world > 1:
-        line["gather"] = {"collective": "2 x ncclAllGather (rgb 12 B/ray, depth 4 B/ray)", "bytes_per_rank_per_frame": n_local * 16}
+        total_ms = sum(ms_dev)
+        value = H * W * args.steps / (total_ms / 1e3)
+        e2e_value = H * W * args.steps / (sum(ms_e2e) / 1e3)
+        flop_per_ray = (2 * N_SAMPLES + N_IMPORTANCE) * FLOP_PER_EVAL
+        roofline = None
+        if precision == "bf16" and mlp_launches > 0 and mlp_ms > 0 and args.fast_sampling is None:
+            # event brackets around every fused-MLP launch of the timed steps, on the launching stream
+            achieved = mlp_rows * FLOP_PER_EVAL / (mlp_ms / 1e3) / 1e12
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": peak_sus, "unit": "TFLOP/s", "frac": achieved / peak_sus,
+                        "traffic": NCU_TRAFFIC_BYTES["render"]["fwd"], "traffic_unit": "bytes per launch (ncu dram read + write, fine-net launch)",
+                        "kernel": "mlp_tc2_forward_kernel (CTA pair, tcgen05 cta_group::2)",
+                        "peak_kind": "%s sustained bf16 (burst %.1f)" % (peak_kind, peak_burst),
+                        "launches_timed": mlp_launches, "avg_launch_ms": mlp_ms / mlp_launches,
+                        "share_of_step": mlp_ms / total_ms if world == 1 else None,
+                        "step_tflops_per_gpu": n_local * flop_per_ray / (total_ms / args.steps / 1e3) / 1e12}
+        line.update({"value": value, "ms_per_step": total_ms / args.steps,
+                     "e2e": {"value": e2e_value, "unit": "rays/s", "h2d_bytes_per_step": H * W * 24, "d2h_bytes_per_step": H * W * 16,
+                             "ms_per_step": sum(ms_e2e) / args.steps,
+                             "api": "nerf_render_rays_host (C ABI, host buffers)" if world == 1 else
+                                    "pinned host rays -> H2D -> Renderer.render (band) -> NCCL all-gather -> D2H of the frame on rank 0"},
+                     "gpu_launches": launches, "clocks": clocks, "roofline": roofline})
+        if world > 1:
+            line["gather"] = {"collective": "2 x ncclAllGather (rgb 12 B/ray, depth 4 B/ray)", "bytes_per_rank_per_frame": n_local * 16}
 
     # ---- secondary: weak scaling (round 1's figure): N views x N bands, 640 000 rays per GPU, no collective ----------------
     if world > 1 and do_render:
@@ -477,17 +479,24 @@ def main():
         if args.mode == "all" and not args.train_rays:
             line["train_c5"] = train_record(args, eng, net, cfg, rank, world, dev, TRAIN_RAYS_C5, timed, barrier, peak_sus, full=False)
 
+    if not do_render and "train" in line:           # --mode train (profiling runs): the line's headline keys carry the train record
+        t = line["train"]
+        line.update({"metric": "rays/sec train (lego, %d rays/rank/step)" % TRAIN_RAYS, "value": t["value"], "ms_per_step": t["ms_per_step"],
+                     "scaling": "weak", "e2e": t.get("e2e"), "gpu_launches": int(t["gpu_launches_per_step"] * t["steps"]), "roofline": None})
+        value = t["value"]
+
     # ---- baselines on rank 0 of a single-GPU run --------------------------------------------------------------------------
     if rank == 0 and world == 1 and not args.no_gpu_baseline and (N_SAMPLES, N_IMPORTANCE) == (64, 128) and args.fast_sampling is None:
         try:
             gb = gpu_baseline()
-            gb["render"]["speedup_of_this_engine"] = value / gb["render"]["value"]
+            if do_render:
+                gb["render"]["speedup_of_this_engine"] = value / gb["render"]["value"]
             if "train" in line:
                 gb["train"]["speedup_of_this_engine"] = line["train"]["value"] / gb["train"]["value"]
             line["gpu_baseline"] = gb
         except Exception as e:                                    # a baseline must never take the headline down with it
             line["gpu_baseline"] = {"kind": "port-cuda", "error": repr(e)}
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and do_render:
         threads = os.cpu_count() or 1
         v, n_done, dt = cpu_render_rate(12.0, threads)
         line["cpu_baseline"] = {"value": v, "unit": "rays/s", "cores": threads, "kind": "port",

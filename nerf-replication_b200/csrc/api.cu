@@ -80,6 +80,7 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   if (h->wpack_bwd) cudaFree(h->wpack_bwd);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   if (h->side) cudaStreamDestroy(h->side);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   if (h->pack_ev) cudaEventDestroy(h->pack_ev);
   if (h->fine_grad_ev) cudaEventDestroy(h->fine_grad_ev);
   if (h->side_fork) cudaEventDestroy(h->side_fork);
@@ -665,12 +666,23 @@ extern "C" int nerf_forward_backward(NerfEngine* h, const float* rays_o, const f
     sg_.key = key; sg_.warm = true;
     return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
   }
-  // second identical call: capture, instantiate, launch
+  // second identical call: capture, instantiate, launch.  The capture runs on a private stream (the caller's may be the
+  // legacy default stream, which cannot be captured); the graph itself is stream-agnostic and is launched on the caller's.
   const int64_t l0 = h->launches;
-  NERF_CUDA_TRY(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-  rc = forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  if (!h->cap_stream && cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    h->graph_mode = false;
+    return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
+  cudaError_t e = cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    h->graph_mode = false;
+    return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
+  rc = forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, h->cap_stream);
   cudaGraph_t graph = nullptr;
-  cudaError_t e = cudaStreamEndCapture(st, &graph);
+  e = cudaStreamEndCapture(h->cap_stream, &graph);
   if (rc || e != cudaSuccess || !graph) {
     if (graph) cudaGraphDestroy(graph);
     cudaGetLastError();

@@ -42,6 +42,7 @@ struct NerfEngine {
   // coarse net's backward starts (nerf_stream_wait_fine_grads)
   cudaEvent_t fine_grad_ev = nullptr;
   bool fine_grad_recorded = false;
+  cudaStream_t cap_stream = nullptr;        // private stream the step graph is captured on
   bool graph_mode = true;                   // nerf_forward_backward may capture / replay the step as a CUDA graph
 
   // host-path resources (nerf_render_rays_host)
