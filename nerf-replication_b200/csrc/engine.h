@@ -1,6 +1,8 @@
 // engine.h -- the opaque handle behind the C ABI and the launchers each .cu file provides.
 #pragma once
+#include <cstdlib>
 #include <map>
+#include <utility>
 #include <string>
 #include <vector>
 #include "common.cuh"
@@ -93,6 +95,21 @@ struct NerfEngine {
 };
 
 namespace nerf {
+
+// Between two persistent tcgen05 kernels (228 KB of shared memory per CTA) a small stage kernel with the default carve-out
+// would make every SM switch its L1 / shared-memory split and back; these kernels stream through L2 anyway, so they ask for
+// the same (maximum shared) split.  NERF_B200_CARVEOUT=0 keeps the driver default (A/B measurements).
+inline void prefer_max_shared(const void* func, int device) {
+  static std::map<std::pair<const void*, int>, bool> done;
+  static int enabled = -1;
+  if (enabled < 0) { const char* v = getenv("NERF_B200_CARVEOUT"); enabled = (v && v[0] == '0') ? 0 : 1; }
+  if (!enabled) return;
+  bool& d = done[std::make_pair(func, device)];
+  if (d) return;
+  d = true;
+  cudaFuncSetAttribute(func, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  cudaGetLastError();
+}
 
 // ---- stages.cu ---------------------------------------------------------------------------------
 struct Camera { float r[9]; float o[3]; double r64[9]; double o64[3]; double focal, cx, cy; int H, W; };

@@ -729,6 +729,7 @@ int mlp_tc2_wgrad(NerfEngine* h, bool full, int64_t M, const float* d_raw, const
   }
   cudaEventRecord(h->side_fork, st);
   cudaStreamWaitEvent(h->side, h->side_fork, 0);
+  prefer_max_shared(reinterpret_cast<const void*>(wgrad_heads_kernel), h->device);
   wgrad_heads_kernel<<<std::min(a.n_tiles, h->num_sms), kHeadThreads, 0, h->side>>>(act_arena, reinterpret_cast<const float4*>(d_raw), M,
                                                                                     a.n_tiles, full ? 1 : 0, flat_grad_net);
   cudaEventRecord(h->side_join, h->side);

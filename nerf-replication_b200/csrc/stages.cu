@@ -76,6 +76,7 @@ void launch_stratified_t(NerfEngine* h, int64_t n, int S, const float* jitter, b
                          float* t, cudaStream_t st) {
   if (n <= 0) return;
   int blocks = (int)std::min<int64_t>((n * S + 255) / 256, (int64_t)h->num_sms * 8);
+  prefer_max_shared(reinterpret_cast<const void*>(stratified_t_kernel), h->device);
   stratified_t_kernel<<<blocks, 256, 0, st>>>(n, S, h->cfg.t_near, h->cfg.t_far, jitter, philox ? 1 : 0,
                                               h->cfg.seed, call_id, t);
   h->launches++;
@@ -177,6 +178,7 @@ __global__ void composite_kernel(const float4* __restrict__ raw, const float* __
 void launch_composite(NerfEngine* h, const float* raw, const float* t, int64_t n, int S, int white,
                       float* rgb, float* depth, float* acc, float* weights, cudaStream_t st) {
   if (n <= 0) return;
+  prefer_max_shared(reinterpret_cast<const void*>(composite_kernel), h->device);
   composite_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, 0, st>>>(
       reinterpret_cast<const float4*>(raw), t, n, S, white, rgb, depth, acc, weights);
   h->launches++;
@@ -445,6 +447,7 @@ int launch_sample_pdf(NerfEngine* h, const float* raw_c, const float* t_c, int64
   if (row_list && (int64_t)n * (Nc + Nf) >= (int64_t)1 << 31) return h->fail(NERF_E_INVALID, "sample_pdf: row list needs n*(Nc+Nf) < 2^31");
   const size_t smem = (size_t)kWarpsPerBlock * pdf_smem_words(Nc, Nf, Npad) * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(sample_pdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  prefer_max_shared(reinterpret_cast<const void*>(sample_pdf_kernel), h->device);
   sample_pdf_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw_c), t_c, n, Nc, Nf, Npad, u, philox_u ? 1 : 0, h->cfg.seed, call_id, cdf_in,
       t_fine, inds, below, above, cdf_out, t_sorted, sort_idx, prune);
@@ -604,6 +607,7 @@ void launch_composite_bwd(NerfEngine* h, const float* raw, const float* t, int64
   if (n <= 0) return;
   const size_t smem = (size_t)kWarpsPerBlock * 3 * S * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(composite_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  prefer_max_shared(reinterpret_cast<const void*>(composite_bwd_kernel), h->device);
   composite_bwd_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw), t, n, S, white, d_rgb_map, d_depth_map, d_w, reinterpret_cast<float4*>(d_raw), d_t);
   h->launches++;
@@ -665,6 +669,7 @@ void launch_composite_loss_bwd(NerfEngine* h, const float* raw, const float* t, 
   const size_t smem = (size_t)kWarpsPerBlock * 3 * S * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(composite_loss_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const float gscale = 2.0f * scale / (3.0f * (float)n);
+  prefer_max_shared(reinterpret_cast<const void*>(composite_loss_bwd_kernel), h->device);
   composite_loss_bwd_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw), t, n, S, white, gt, gscale, rgb_out, reinterpret_cast<float4*>(d_raw), d_t, sq, done, loss);
   h->launches++;
@@ -761,6 +766,7 @@ int launch_sample_pdf_bwd(NerfEngine* h, const float* raw_c, const float* t_c, i
   const int Npad = next_pow2(Nc + Nf);
   const size_t smem = (size_t)kWarpsPerBlock * (2 * Nc + 2 * Npad + Nc + Nf + (d_raw_c ? 3 * Nc : 0)) * sizeof(float);
   if (smem > 48 * 1024) cudaFuncSetAttribute(sample_pdf_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  prefer_max_shared(reinterpret_cast<const void*>(sample_pdf_bwd_kernel), h->device);
   sample_pdf_bwd_kernel<<<grid_for(n, h->num_sms), kWarpsPerBlock * 32, smem, st>>>(
       reinterpret_cast<const float4*>(raw_c), t_c, n, Nc, Nf, Npad, u, philox_u ? 1 : 0, h->cfg.seed, call_id,
       d_t_sorted, sort_idx, d_w_coarse, white, reinterpret_cast<float4*>(d_raw_c));

@@ -4,6 +4,7 @@
     python profiles/summarize.py launches gpurun_out/launches_r1.csv  > profiles/launches_r1.txt
     python profiles/summarize.py raw      gpurun_out/prof_mlp_r1.ncu-rep > profiles/mlp_r1_metrics.txt
     python profiles/summarize.py source   gpurun_out/prof_mlp_r1.ncu-rep > profiles/mlp_r1_hot_sass.txt
+    python profiles/summarize.py stages   gpurun_out/stages_render_r2a.csv > profiles/stages_render_r2_metrics.txt
 """
 import collections
 import csv
@@ -46,6 +47,38 @@ def launches(path):
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print("%-60s %6d %12.3f %6.1f%%" % (k[:60], v[0], v[1], 100 * v[1] / tot))
     print("%-60s %6d %12.3f" % ("TOTAL", sum(v[0] for v in agg.values()), tot))
+
+
+def stages(path):
+    """Launch list taken with --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum: per kernel the
+    number of launches, mean duration and mean DRAM bytes read / written per launch, and the DRAM rate they imply."""
+    rows = list(csv.reader(open(path)))
+    hdr = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
+    H, data = rows[hdr], rows[hdr + 1:]
+    ii, ki, mi, vi, ui = H.index("ID"), H.index("Kernel Name"), H.index("Metric Name"), H.index("Metric Value"), H.index("Metric Unit")
+    tscale = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6}
+    bscale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = collections.OrderedDict()            # launch id -> {kernel, us, rd, wr}
+    for r in data:
+        if len(r) <= vi:
+            continue
+        d = per.setdefault(r[ii], {"k": r[ki].split("(")[0], "us": 0.0, "rd": 0.0, "wr": 0.0})
+        v = float(r[vi].replace(",", ""))
+        if r[mi].startswith("gpu__time_duration"):
+            d["us"] = v * tscale[r[ui]]
+        elif r[mi].startswith("dram__bytes_read"):
+            d["rd"] = v * bscale[r[ui]]
+        elif r[mi].startswith("dram__bytes_write"):
+            d["wr"] = v * bscale[r[ui]]
+    agg = collections.OrderedDict()
+    for d in per.values():
+        a = agg.setdefault(d["k"], [0, 0.0, 0.0, 0.0])
+        a[0] += 1; a[1] += d["us"]; a[2] += d["rd"]; a[3] += d["wr"]
+    print("# ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none: %s" % path)
+    print("# per launch means (cold-cache, serialised launches); DRAM GB/s = (read + write) / duration")
+    print("%-56s %5s %10s %12s %12s %10s" % ("kernel", "n", "us", "dram rd MB", "dram wr MB", "GB/s"))
+    for k, (n, us, rd, wr) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print("%-56s %5d %10.2f %12.3f %12.3f %10.1f" % (k[:56], n, us / n, rd / n / 1e6, wr / n / 1e6, (rd + wr) / max(us, 1e-9) / 1e3))
 
 
 def raw(rep):
@@ -94,9 +127,9 @@ def lines(rep, launch="0", top=40):
             out.append((int(n) if n.isdigit() else 0, path, r[0], r[1].strip()))
     tot = sum(o[0] for o in out) or 1
     print("# ncu source page, CUDA lines by samples (launch %s: %s): %d samples" % (launch, fn[:70], tot))
-    for n, f, ln, src in sorted(out, reverse=True)[:top]:
+    for n, f, ln, src in sorted(out, reverse=True)[:int(top)]:
         print("%6.2f%%  %s:%s  %s" % (100 * n / tot, f, ln, src[:110]))
 
 
 if __name__ == "__main__":
-    {"launches": launches, "raw": raw, "source": source, "lines": lines}[sys.argv[1]](*sys.argv[2:])
+    {"launches": launches, "stages": stages, "raw": raw, "source": source, "lines": lines}[sys.argv[1]](*sys.argv[2:])

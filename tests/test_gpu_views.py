@@ -2,9 +2,12 @@
 configs[3]: 128+256) of Renderer.render (volume_renderer.py:290-432) against the oracle, with the measured error
 distributions kept: every run writes gpurun_out/parity_views.json (committed copy: profiles/parity_c1_r2.json).
 
-Oracle arm: oracle/nerf_oracle.py with its tensors on the GPU (fp32 cuBLAS, TF32 off) -- first checked here against the
-same file on the CPU, which is pinned bit-exactly to the executed reference (tests/golden).  fp32 engine vs the oracle on
-the same weights; bf16 engine vs the oracle on the same bf16-representable weights.
+Oracle arm: oracle/nerf_oracle.py on the CPU -- the restatement pinned bit-exactly to the executed reference (tests/golden).
+fp32 engine vs the oracle on the same weights; bf16 engine vs the oracle on the same bf16-representable weights.
+For scale, the report also carries "reference_self_noise_cuda_vs_cpu": the SAME oracle run on the GPU (cuBLAS fp32, TF32
+off) against itself on the CPU -- the reference's own GPU path differs from its CPU path by more than north_star's 1e-5 on
+some rays (measured on B200: rgb 1.1e-5 .. 2.3e-5 max), because a different GEMM accumulation order flips searchsorted
+indices in near-empty bins.
 
 Gates (north_star: rgb 1e-5 fp32 / 1e-3 bf16): rgb on ALL rays of the view, no ray excused, except that a bounded number
 of rays may exceed the gate and that number is asserted and reported (an index flip of searchsorted in a near-empty bin, or
@@ -39,13 +42,15 @@ def _write_report():
         json.dump(REPORT, f, indent=1, sort_keys=True)
 
 
-def _oracle_cuda(oracle, sd, ro, rd, **kw):
+def _oracle(oracle, sd, ro, rd, device="cpu", **kw):
+    """-> the oracle's taps as CUDA tensors (computed on `device`: "cpu" = the pinned arithmetic)."""
     torch.backends.cuda.matmul.allow_tf32 = False
-    sd_d = {k: v.cuda() for k, v in sd.items()}
+    torch.set_num_threads(os.cpu_count() or 8)
+    sd_d = {k: v.to(device) for k, v in sd.items()}
     taps = {}
     with torch.no_grad():
-        oracle.render(sd_d, ro.cuda(), rd.cuda(), taps=taps, **kw)
-    return taps
+        oracle.render(sd_d, ro.to(device), rd.to(device), taps=taps, **kw)
+    return {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in taps.items()}
 
 
 def _pose(oracle, name):
@@ -79,14 +84,16 @@ def test_full_c1_view_parity(oracle, pose, weights):
     H = W = 100
     ro, rd = (torch.from_numpy(x) for x in oracle.get_rays_np(_pose(oracle, pose), H, W))
     sd = oracle.init_state_dict(0, sharp=(weights == "sharp"))
-    # the GPU oracle arm runs the same algorithm as the pinned CPU oracle (first 256 rays)
-    taps = _oracle_cuda(oracle, sd, ro, rd)
-    with torch.no_grad():
-        rgb_cpu, dep_cpu = oracle.render(sd, ro[:256], rd[:256])
-    assert float((taps["rgb_map"][:256].cpu() - rgb_cpu).abs().max()) <= 2e-6
+    taps = _oracle(oracle, sd, ro, rd)
+    # yardstick: the same oracle on the GPU vs on the CPU (the reference's own CUDA-vs-CPU distance)
+    tg = _oracle(oracle, sd, ro, rd, device="cuda")
+    REPORT["reference_self_noise_cuda_vs_cpu_%s_%s" % (pose, weights)] = {
+        "rays": H * W, "rgb": _q((tg["rgb_map"] - taps["rgb_map"]).abs().amax(-1)), "depth": _q((tg["depth_map"] - taps["depth_map"]).abs()),
+        "rays_over_1e-5_rgb": int(((tg["rgb_map"] - taps["rgb_map"]).abs().amax(-1) > 1e-5).sum()),
+        "inds_flips": int((tg["inds"] != taps["inds"]).sum()), "inds_total": int(taps["inds"].numel())}
     for precision in ("fp32", "bf16"):
         sd_p = sd if precision == "fp32" else oracle.round_weights_bf16(sd)
-        tp = taps if precision == "fp32" else _oracle_cuda(oracle, sd_p, ro, rd)
+        tp = taps if precision == "fp32" else _oracle(oracle, sd_p, ro, rd)
         eng = make_engine(oracle, sd_p, precision)
         out = eng.render_rays(ro.cuda(), rd.cuda(), full=True)
         torch.cuda.synchronize()
@@ -109,7 +116,7 @@ def test_c4_samples_4096_rays(oracle):
     ro, rd = (torch.from_numpy(x) for x in oracle.get_rays_np(oracle.lego_pose(0), 800, 800, pix))
     for precision in ("fp32", "bf16"):
         sd_p = sd if precision == "fp32" else oracle.round_weights_bf16(sd)
-        tp = _oracle_cuda(oracle, sd_p, ro, rd, n_samples=128, n_importance=256)
+        tp = _oracle(oracle, sd_p, ro, rd, n_samples=128, n_importance=256)
         eng = make_engine(oracle, sd_p, precision, n_samples=128, n_importance=256)
         out = eng.render_rays(ro.cuda(), rd.cuda(), full=True)
         torch.cuda.synchronize()
