@@ -30,7 +30,8 @@ constexpr int kActHV = 38;       // views hidden (post-ReLU), 2 blocks
 constexpr int kActBlocks = 40;
 // ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][word 0..7][row 0..127] uint32 (a warp's
 //      word store / load covers 128 contiguous bytes); word w of a row covers columns [32 w, 32 w + 32):
-//      bit i = column 32 w + 2 i, bit 16 + i = column 32 w + 2 i + 1
+//      column pair i (columns 32 w + 2 i, + 1) has its two flags at bits 8 (i & 1) + 7 - (i >> 1) and that + 16
+//      (tc_common.cuh pos_bits32 / mask2_from_bits: the consumer expands a pair with one shift-shared PRMT)
 constexpr int kMaskH = 0;        // h_l > 0, l = 0..7
 constexpr int kMaskHV = 8;       // views hidden > 0 (words 0..3)
 constexpr int kMaskLayers = 9;

@@ -201,15 +201,24 @@ __device__ __forceinline__ uint32_t pos_mask2(uint32_t h) {
   asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(h), "r"(z));
   return d;
 }
-// 16 bf16x2 words (32 columns) -> one mask word: bit i = low half of word i positive, bit 16 + i = high half (tc_arena.cuh)
+// 16 bf16x2 words (32 columns) -> one mask word.  Bit layout chosen for the consumer (mask2_from_bits): with k = i >> 1 and
+// b = i & 1, the flag of word i's low half is bit 8 b + 7 - k and the flag of its high half bit 8 (b + 2) + 7 - k, so that
+// (bits << k) carries both flags in the sign bits of bytes b and b + 2.
 __device__ __forceinline__ uint32_t pos_bits32(const uint32_t (&pk)[16]) {
   uint32_t m = 0;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) m |= pos_mask2(pk[i]) & (0x00010001u << i);
+  for (int i = 0; i < 16; ++i) m |= pos_mask2(pk[i]) & (0x00010001u << (8 * (i & 1) + 7 - (i >> 1)));
   return m;
 }
-// inverse for one word: 0xFFFF in the halves whose bits (i, 16 + i) are set
-__device__ __forceinline__ uint32_t mask2_from_bits(uint32_t bits, int i) { return ((bits >> i) & 0x00010001u) * 0xFFFFu; }
+// inverse for one word: 0xFFFF in the halves whose flags are set -- one shift per word pair and one PRMT in sign-replicate
+// mode (selector nibble 8 | byte) instead of shift + and + multiply
+__device__ __forceinline__ uint32_t mask2_from_bits(uint32_t bits, int i) {
+  uint32_t d;
+  const uint32_t m = bits << (i >> 1);
+  if (i & 1) asm("prmt.b32 %0, %1, %1, 0xBB99;" : "=r"(d) : "r"(m));
+  else asm("prmt.b32 %0, %1, %1, 0xAA88;" : "=r"(d) : "r"(m));
+  return d;
+}
 // streaming 16-byte global store (written once, read by a later kernel after far more than L2-size traffic)
 __device__ __forceinline__ void st_global_cs(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
