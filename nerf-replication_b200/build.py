@@ -53,6 +53,12 @@ def up_to_date(out=OUT, sources=SOURCES):
     return os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == _digest(sources)
 
 
+def build_experiment(bits, verbose=False):
+    """Diagnostic flavour libnerf_b200_exp<bits>.so (-DNERF_EXP=bits: timing experiments that break results on purpose, see
+    csrc/tc_common.cuh); select it with NERF_B200_LIB=<path>.  Never the product library."""
+    return _build(OUT.replace(".so", "_exp%d.so" % bits), os.path.join(HERE, "build_exp%d" % bits), SOURCES, ["-DNERF_EXP=%d" % bits], verbose)
+
+
 def build(force=False, verbose=False, waitprof=False):
     """waitprof=True builds the diagnostic flavour libnerf_b200_waitprof.so (-DNERF_TC_WAITPROF: every barrier wait of the
     CTA-pair kernels is timed); select it with NERF_B200_LIB=<path>.  The product library never carries that code."""
@@ -97,4 +103,7 @@ def _build(out, objdir, sources, extra, verbose):
 
 
 if __name__ == "__main__":
+    if "--exp" in sys.argv:
+        print(build_experiment(int(sys.argv[sys.argv.index("--exp") + 1]), verbose=True))
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose=True, waitprof="--waitprof" in sys.argv))

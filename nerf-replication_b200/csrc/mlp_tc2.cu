@@ -361,7 +361,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
               }
               for (int kb = 0; kb < nkb; ++kb, ++it) {
                 const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-                mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+                if (!(NERF_EXP & 2)) mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
                 tc_fence_after();
                 issue(tile, kb, slot);
                 umma_commit2_w(&sb.w_empty[slot], 0x3);

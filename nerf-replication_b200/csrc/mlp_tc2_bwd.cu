@@ -216,7 +216,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             tc_fence_after();
             for (int kb = 0; kb < nkb; ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
-              mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
+              if (!(NERF_EXP & 2)) mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
               tc_fence_after();
               const uint32_t a_base = sA + tile * 65536u + (uint32_t)kb * 16384u;
               const uint32_t b_base = sW + slot * kHalfBytes;
@@ -246,18 +246,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
     uint32_t lc = 0;
+    // ReLU bit masks of this row (saved by the forward; tc_arena.cuh).  The epilogues are the critical path of this kernel,
+    // so a mask is fetched one step AHEAD of its use (mw_pre: the next step's words, or the next super-tile's init mask): a
+    // load issued just before the accumulator wait would expose its full HBM latency every step.
+    auto load_mask_at = [&](int64_t st_, int layer, uint32_t (&mw)[8]) {
+      const int64_t T_ = (st_ * 2 + rank) * 2 + tile;
+      const uint8_t* mp = a.act_arena + (size_t)T_ * arena::act_tile_bytes() + arena::act_mask_offset() + row * 4 + layer * arena::kMaskLayerBytes;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) mw[w] = (NERF_EXP & 4) ? 0xFFFFFFFFu : __ldg(reinterpret_cast<const uint32_t*>(mp + w * arena::kMaskWordStride));
+    };
+    uint32_t mw_pre[8];
+    if (pair0 < a.n_pair) load_mask_at(pair0, kInitMask, mw_pre);
     for (int64_t st = pair0; st < a.n_pair; st += pair_stride) {
       const int64_t T = (st * 2 + rank) * 2 + tile;
       const int64_t g = T * kTile + row;
       const bool valid = g < a.M;
-      // this row's slice of the tile's gradient-arena blocks and of its saved ReLU bit masks
+      // this row's slice of the tile's gradient-arena blocks
       uint8_t* grow0 = a.grad_arena + (size_t)T * arena::grad_tile_bytes() + arena::cm_row_offset(row);
-      const uint8_t* mrow0 = a.act_arena + (size_t)T * arena::act_tile_bytes() + arena::act_mask_offset() + row * 4;
-      auto load_mask = [&](int layer, uint32_t (&mw)[8]) {
-        const uint8_t* mp = mrow0 + layer * arena::kMaskLayerBytes;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) mw[w] = __ldg(reinterpret_cast<const uint32_t*>(mp + w * arena::kMaskWordStride));
-      };
       const float4 dr = valid ? __ldg(a.d_raw + g) : make_float4(0.f, 0.f, 0.f, 0.f);
       float p[3] = {0.f, 0.f, 0.f}, vd[3];
       if (FINE && valid) row_point(a.src, g, p, vd);
@@ -265,7 +270,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       // ---- init: the first A operand from d raw ----
       {
         uint32_t mw[8];
-        load_mask(kInitMask, mw);
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mw[w] = mw_pre[w];
+        if (step_mask_layer(step_at(0)) >= 0) load_mask_at(st, step_mask_layer(step_at(0)), mw_pre);     // for the first step
         uint8_t* grow = grow0 + (size_t)(FINE ? arena::kGradHV : arena::kGradZ + 28) * arena::kBlockBytes;
 #pragma unroll
         for (int c32 = 0; c32 < 2 * kInitBlocks; ++c32) {
@@ -289,8 +296,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 
       for (int i = 0; i < kSteps; ++i, ++lc) {
         const int s = step_at(i);
-        uint32_t mw_next[8];
-        if (step_mask_layer(s) >= 0) load_mask(step_mask_layer(s), mw_next);     // in flight while the MMAs finish
+        uint32_t mw_next[8];                      // this step's mask words (fetched during the previous step)
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mw_next[w] = mw_pre[w];
+        if (i + 1 < kSteps) {
+          if (step_mask_layer(step_at(i + 1)) >= 0) load_mask_at(st, step_mask_layer(step_at(i + 1)), mw_pre);
+        } else if (st + pair_stride < a.n_pair) {
+          load_mask_at(st + pair_stride, kInitMask, mw_pre);
+        }
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
         if (s == S_PE5) {

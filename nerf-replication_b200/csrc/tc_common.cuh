@@ -220,7 +220,13 @@ __device__ __forceinline__ uint32_t mask2_from_bits(uint32_t bits, int i) {
   return d;
 }
 // streaming 16-byte global store (written once, read by a later kernel after far more than L2-size traffic)
+// NERF_EXP (diagnostic builds only, build.py --exp N; never defined in the product library): timing experiments that break
+// results on purpose -- bit 0: no arena stores, bit 1: MMA issuers do not wait for weight stages, bit 2: dgrad loads no masks
+#ifndef NERF_EXP
+#define NERF_EXP 0
+#endif
 __device__ __forceinline__ void st_global_cs(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  if (NERF_EXP & 1) return;
   asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
