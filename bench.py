@@ -537,8 +537,8 @@ def train_record(args, eng, net0, cfg, rank, world, dev, n_rays, timed, barrier,
         trainer.step(*dev_b[i % nb])
 
     def step_e2e(i):
-        o, d, gt = (t.to(dev, non_blocking=True) for t in host_b[i % nb])
-        loss_host.copy_(trainer.step(o, d, gt), non_blocking=True)
+        # pinned host batch straight into the step call (the engine stages it: 3 H2D copies), loss read back every step
+        loss_host.copy_(trainer.step(*host_b[i % nb]), non_blocking=True)
 
     flop_step = n_rays * train_flop_per_ray()
     mark = {}
@@ -557,7 +557,7 @@ def train_record(args, eng, net0, cfg, rank, world, dev, n_rays, timed, barrier,
     ms_e2e = timed(step_e2e, steps, warm, "wall")
     rec["e2e"] = {"value": n_rays * world / (sum(ms_e2e) / steps / 1e3), "unit": "rays/s", "ms_per_step": sum(ms_e2e) / steps,
                   "h2d_bytes_per_step": n_rays * 36 * world, "d2h_bytes_per_step": 4 * world,
-                  "api": "FusedTrainer.step with pinned host batches (H2D inside), loss read back every step"}
+                  "api": "FusedTrainer.step on pinned host batches (nerf_forward_backward stages them: H2D inside), loss read back every step"}
     # per-kernel-class times: plain launches with event brackets around the MLP kernels (no graph while profiling)
     teng.profile(True)
     teng.profile_read()
@@ -647,6 +647,7 @@ def dp_grad_check(trainer, eng, my_batch, world, n_rays):
                              "g_single = one process on the %d concatenated rays" % (world, n_rays, world * n_rays)}
     for name, sl in (("coarse_net", slice(0, half)), ("fine_net", slice(half, None))):
         scale = float(g_one[sl].abs().max())
+        out[name + "_max_abs_grad"] = scale
         out[name + "_max_rel_err"] = float((g_dp[sl] - g_one[sl]).abs().max()) / max(scale, 1e-30)
     out["ok"] = bool(out["coarse_net_max_rel_err"] <= 2e-4 and out["fine_net_max_rel_err"] <= 2e-4)
     eng.forward_backward(o, d, gt, trainer.net.flat_grad, grad_scale=1.0 / world)       # leave the engine's buffers at the per-rank size

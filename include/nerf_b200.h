@@ -142,7 +142,9 @@ int nerf_render_rays_host(NerfEngine* h, const float* rays_o_host, const float* 
 /* ---- training: trainers/nerf.py:27-33 (MSE), trainer.py:56-60, train/optimizer.py:8-28 ------------- */
 /* loss = mean((render(rays)-rgb_gt)^2); writes d loss/d params * grad_scale into flat_grad (overwritten,
  * not accumulated), loss into *loss (device float).  Follows the reference autograd graph incl. the
- * un-detached t_fine path. */
+ * un-detached t_fine path.  rays_o / rays_d / rgb_gt [n,3] may be device OR host arrays (they are
+ * copied into engine-owned staging buffers first; pinned host memory keeps the copy asynchronous); all other pointers
+ * are device pointers. */
 int nerf_forward_backward(NerfEngine* h, const float* rays_o, const float* rays_d, const float* rgb_gt,
                           int64_t n, const float* jitter, const float* u, float grad_scale,
                           float* loss, float* flat_grad, float* rgb_out, void* stream);

@@ -84,7 +84,7 @@ int launch_clip_adam_pack(NerfEngine* h, float* p, const float* g, float* m, flo
   int64_t n4 = n / 4;
   float step_size = sc.step_size, inv = sc.inv_bc2_sqrt;
   void* args[] = {&p4, &g4, &m4, &v4, &n4, &b1, &b2, &step_size, &inv, &eps, &clip, &wpack, &slabs, &wpack_bwd};
-  const int grid = h->num_sms * std::min(bps, 4);     // every CTA resident: the grid barrier needs it
+  const int grid = h->num_sms * std::min(bps, 8);     // every CTA resident: the grid barrier needs it
   prefer_max_shared(reinterpret_cast<const void*>(clip_adam_pack_kernel), h->device);
   cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(clip_adam_pack_kernel), dim3(grid), dim3(256), args, 0, st);
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("clip_adam_pack launch: ") + cudaGetErrorString(e));

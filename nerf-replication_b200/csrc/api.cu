@@ -641,17 +641,23 @@ extern "C" int nerf_forward_backward(NerfEngine* h, const float* rays_o, const f
   const bool philox = (c.perturb && !jitter) || (c.train_u && !u && c.n_importance > 0);
   cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
   cudaStreamIsCapturing(st, &cs);
-  if (!h->graph_mode || philox || h->profiling || cs != cudaStreamCaptureStatusNone) {
-    return forward_backward_body(h, rays_o, rays_d, rgb_gt, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
-  }
-  // stage the inputs (no-op when the caller already uses the staging buffers, e.g. nerf_bank_train_step)
+  // Stage the inputs in engine-owned buffers (no-op when the caller already uses them, e.g. nerf_bank_train_step).  The
+  // copies take the direction from the pointers (unified addressing), so rays_o / rays_d / rgb_gt may also be HOST arrays
+  // (pinned for an asynchronous copy): the end-to-end path then needs no device tensors of its own.
   float *so, *sd, *sg;
   int rc;
   if ((rc = h->buf("bank.o", (size_t)n * 3, &so)) || (rc = h->buf("bank.d", (size_t)n * 3, &sd)) || (rc = h->buf("bank.c", (size_t)n * 3, &sg))) return rc;
-  const size_t bytes = (size_t)n * 3 * sizeof(float);
-  if (rays_o != so) NERF_CUDA_TRY(h, cudaMemcpyAsync(so, rays_o, bytes, cudaMemcpyDeviceToDevice, st));
-  if (rays_d != sd) NERF_CUDA_TRY(h, cudaMemcpyAsync(sd, rays_d, bytes, cudaMemcpyDeviceToDevice, st));
-  if (rgb_gt != sg) NERF_CUDA_TRY(h, cudaMemcpyAsync(sg, rgb_gt, bytes, cudaMemcpyDeviceToDevice, st));
+  if (cs == cudaStreamCaptureStatusNone) {
+    const size_t bytes = (size_t)n * 3 * sizeof(float);
+    if (rays_o != so) NERF_CUDA_TRY(h, cudaMemcpyAsync(so, rays_o, bytes, cudaMemcpyDefault, st));
+    if (rays_d != sd) NERF_CUDA_TRY(h, cudaMemcpyAsync(sd, rays_d, bytes, cudaMemcpyDefault, st));
+    if (rgb_gt != sg) NERF_CUDA_TRY(h, cudaMemcpyAsync(sg, rgb_gt, bytes, cudaMemcpyDefault, st));
+  } else {
+    so = const_cast<float*>(rays_o); sd = const_cast<float*>(rays_d); sg = const_cast<float*>(rgb_gt);   // caller captures: device pointers as given
+  }
+  if (!h->graph_mode || philox || h->profiling || cs != cudaStreamCaptureStatusNone) {
+    return forward_backward_body(h, so, sd, sg, n, jitter, u, grad_scale, loss, flat_grad, rgb_out, st);
+  }
   StepKey key{n, jitter, u, loss, flat_grad, rgb_out, h->params, grad_scale, c};
   StepGraph& sg_ = g_step_graphs[h];
   if (sg_.exec && sg_.key == key) {

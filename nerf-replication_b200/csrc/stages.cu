@@ -112,11 +112,10 @@ void launch_freq_encode(NerfEngine* h, const float* x, int64_t m, int n_freqs, f
 // ------------------------------------------------------------------------------------------------
 // Per-sample transmittance pieces, evaluated exactly like weights_computation (volume_renderer.py:80-94):
 //   delta_i = t_{i+1}-t_i (last 1e10);  e = exp(-sigma*delta);  alpha = 1-e;  q = clamp(1-alpha, 1e-10, 1)
-// exp / sigmoid rounded from a double-precision evaluation: within 0.5 ulp(fp32), which is what the CPU
+// exp rounded from a double-precision evaluation: within 0.5 ulp(fp32), which is what the CPU
 // libm of the reference delivers in ~99% of calls (CUDA's expf is 2 ulp).  alpha = 1 - exp(-sigma delta)
 // cancels catastrophically at sigma delta ~ 1e-3, so 1 ulp of exp is 1e-4 relative in the sampling pdf.
 __device__ __forceinline__ float exp_cr(float x) { return (float)exp((double)x); }
-__device__ __forceinline__ float sigmoid_cr(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, exp_cr(-x))); }
 // colours: sigmoid is well conditioned (no cancellation), MUFU.EX2 accuracy (|err| < 4e-7 for |x| < 20) is far inside the
 // 1e-5 gate; three of the four double-precision exp calls per sample of the forward composite go away
 __device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
@@ -529,6 +528,9 @@ __device__ __forceinline__ void composite_bwd_ray(const float4* __restrict__ rr,
                                                   const float* sT, const float* sA, float* sD) {
   const int nblk = (S + 31) / 32;
   const float wb = white ? 1.0f : 0.0f;
+  // no colour gradient arrives at the coarse pass of the hierarchical step (only d w through the inverse CDF): skip the
+  // three sigmoids per sample there (per-ray condition, uniform across the warp)
+  const bool need_rgb = (g0 != 0.f) || (g1 != 0.f) || (g2 != 0.f);
   // suffix sums S_k = sum_{j>k} dw_j w_j
   float suffix_carry = 0.f;
   for (int j = nblk - 1; j >= 0; --j) {
@@ -537,7 +539,8 @@ __device__ __forceinline__ void composite_bwd_ray(const float4* __restrict__ rr,
     float4 v = valid ? __ldg(rr + i) : make_float4(0.f, 0.f, 0.f, 0.f);
     const float T = valid ? sT[i] : 0.f, alpha = valid ? sA[i] : 0.f;
     const float w = T * alpha;
-    const float c0 = sigmoid_cr(v.x), c1 = sigmoid_cr(v.y), c2 = sigmoid_cr(v.z);
+    // the same sigmoid the forward composite evaluates (MUFU.EX2, |err| < 4e-7): the backward differentiates what was rendered
+    const float c0 = need_rgb ? sigmoid_fast(v.x) : 0.f, c1 = need_rgb ? sigmoid_fast(v.y) : 0.f, c2 = need_rgb ? sigmoid_fast(v.z) : 0.f;
     float dw = g0 * (c0 - wb) + g1 * (c1 - wb) + g2 * (c2 - wb) + gd * (valid ? __ldg(tt + i) : 0.f);
     if (d_w_in && valid) dw += d_w_in[i];
     // inclusive suffix scan of dw*w over the lanes of this block

@@ -240,10 +240,19 @@ class Engine:
         """One fused step body: flat_grad = grad_scale * d MSE / d params (overwritten), -> loss (device scalar).  Passing the
         same ``loss`` / ``flat_grad`` tensors (and n) on every call lets the engine replay the step as one CUDA graph."""
         n = rays_o.shape[0]
-        loss = torch.empty((), device=rays_o.device) if loss is None else loss
-        rgb = torch.empty(n, 3, device=rays_o.device) if want_rgb else None
-        self._check(self.lib.nerf_forward_backward(self.h, self._p(rays_o, name="rays_o"), self._p(rays_d, name="rays_d"),
-                                                   self._p(rgb_gt, name="rgb_gt"), n, self._p(jitter, name="jitter"),
+        dev = "cuda:%d" % self.device
+        loss = torch.empty((), device=dev) if loss is None else loss
+        rgb = torch.empty(n, 3, device=dev) if want_rgb else None
+
+        def inp(t, name):        # rays / colours: CUDA tensors, or (pinned) host tensors that the engine stages itself
+            if t.is_cuda:
+                return self._p(t, name=name)
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                raise EngineError("%s must be a contiguous fp32 tensor" % name)
+            return t.data_ptr()
+
+        self._check(self.lib.nerf_forward_backward(self.h, inp(rays_o, "rays_o"), inp(rays_d, "rays_d"),
+                                                   inp(rgb_gt, "rgb_gt"), n, self._p(jitter, name="jitter"),
                                                    self._p(u, name="u"), float(grad_scale), loss.data_ptr(),
                                                    self._p(flat_grad, name="flat_grad"),
                                                    None if rgb is None else rgb.data_ptr(), self._stream()))

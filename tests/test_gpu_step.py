@@ -80,6 +80,21 @@ def test_step_graph_replay_matches_plain_launches(oracle):
     eng.close()
 
 
+def test_step_accepts_host_batches(oracle):
+    """nerf_forward_backward stages rays / colours itself: (pinned) host tensors give the same step as device tensors."""
+    sd = oracle.round_weights_bf16(oracle.fog_state_dict(0))
+    eng = make_engine(oracle, sd, "bf16")
+    o, d, gt = _batch(oracle, 2, 200)
+    loss, grad = torch.zeros((), device="cuda"), torch.zeros(2 * P, device="cuda")
+    eng.forward_backward(o, d, gt, grad, loss=loss)
+    l_dev, g_dev = float(loss), grad.clone()
+    for rep in range(3):                       # plain, capture, replay
+        eng.forward_backward(o.cpu().pin_memory(), d.cpu().pin_memory(), gt.cpu().pin_memory(), grad, loss=loss)
+        torch.cuda.synchronize()
+        assert float(loss) == l_dev and _rel(grad[P:], g_dev[P:]) <= 2e-5
+    eng.close()
+
+
 def test_backward_of_an_overwritten_forward_raises(oracle):
     """The handle keeps the activations of ONE forward: a backward for an older forward must fail loudly."""
     from nerf_replication_b200.engine import EngineError
