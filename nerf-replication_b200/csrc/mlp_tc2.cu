@@ -40,14 +40,17 @@ constexpr int kRowsPerCta = 2 * kTile;          // X + Y
 constexpr int kRowsPerPair = 2 * kRowsPerCta;   // 512
 // (a packed stage image is 256 rows x 128 B = 32 KB, both halves: mlp_tc.cu pack_weights_kernel; the tensor maps address it by rows)
 constexpr int kHalfBytes = 16384;               // this CTA's half of a 256-row stage (views layer: 8192)
-constexpr int kRing = 3;
+constexpr int kRingReal = 3;
+// diagnostic builds (NERF_EXP bits 3-4): 1 or 2 extra ring slots ALIASED onto the PE buffers -- wrong results, but it times a
+// deeper weight ring before shared memory is found for one
+constexpr int kRing = kRingReal + ((NERF_EXP >> 3) & 3);
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
 constexpr int kNumStages = 39;
 constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 168 registers per thread
 constexpr int kOnesBytes = 4096;                // constant A slab of the bias MMA: 128 rows x 16 k, columns 0..2 = 1.0
 constexpr int kBiasSlabBytes = 8192;            // packed bias slab of one schedule entry (both halves), mlp_tc.cu pack_bias_slabs_kernel
 constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
-constexpr uint32_t kOffBias = kOffW + kRing * kHalfBytes;         // 212992
+constexpr uint32_t kOffBias = kOffW + kRingReal * kHalfBytes;     // 212992
 constexpr int kBiasRing = 2;                                      // bias slabs have their own small ring (4 KB slots)
 constexpr uint32_t kOffBiasRing = kOffBias + kOnesBytes;          // 217088
 constexpr uint32_t kOffHeads = kOffBiasRing + kBiasRing * 4096;   // 225280: w_alpha[256] | w_rgb[384]
@@ -63,6 +66,8 @@ __host__ __device__ constexpr int sched_start(int li) {
 static_assert(sched_start(kNumSched) == kNumStages, "stage count");
 __host__ __device__ constexpr int sched_n(int li) { return li == 9 ? 128 : 256; }
 __host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li == 8 ? L_FEAT : L_VIEWS); }
+
+__host__ __device__ constexpr uint32_t ring_slot_off(uint32_t slot) { return slot < kRingReal ? kOffW + slot * kHalfBytes : kOffPE + (slot - kRingReal) * kHalfBytes; }
 
 struct Bars {
   uint64_t w_full[kRing], w_empty[kRing], b_full[kBiasRing], b_empty[kBiasRing], acc_full[2], act_ready[2];
@@ -124,7 +129,30 @@ __device__ __forceinline__ void store_pe_block(uint8_t* blk, uint32_t row_base, 
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     if (grow) st_global_cs(grow + c * 1024, pe[4 * c], pe[4 * c + 1], pe[4 * c + 2], pe[4 * c + 3]);
-    store_chunk(blk, row_base, row_xor, c, pe[4 * c], pe[4 * c + 1], pe[4 * c + 2], pe[4 * c + 3]);
+    if (blk) store_chunk(blk, row_base, row_xor, c, pe[4 * c], pe[4 * c + 1], pe[4 * c + 2], pe[4 * c + 3]);
+  }
+}
+
+// Experiment kept behind NERF_DEFER_STORES (default 0 = off): write the arena copy of a finished layer AFTER the tile has
+// been handed back to the MMA issuer, by re-reading the row's 4 x 128 bytes from the swizzled A operand (untouched until
+// the same threads run the tile's next epilogue), to take the 32 st.global.v4 per row and the proxy fence behind them off
+// the MMA -> epilogue -> MMA chain (without any arena store the forward is 10 % and the dgrad chain 21 % faster).
+// Measured on B200: SLOWER (forward 0.400 -> 0.426 ms, dgrad 0.348 -> 0.368 ms per 1024-ray step): the extra 64 KB of
+// shared-memory reads per tile and layer compete with the tensor core's operand fetch (SS-mode MMAs read 64 B/clk of the
+// 128 B/clk the SM has) -- the same reason the bulk shared->global store variant of round 1 lost.
+#ifndef NERF_DEFER_STORES
+#define NERF_DEFER_STORES 0
+#endif
+__device__ __forceinline__ void flush_row_to_arena(const uint8_t* sAct, uint32_t row_base, uint32_t row_xor, uint8_t* grow, int n_blocks) {
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    if (b < n_blocks) {
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        const uint4 v = *reinterpret_cast<const uint4*>(sAct + b * 16384 + row_base + (((uint32_t)ch ^ row_xor) << 4));
+        st_global_cs(grow + b * 16384 + ch * 1024, v.x, v.y, v.z, v.w);
+      }
+    }
   }
 }
 
@@ -135,7 +163,7 @@ __device__ __forceinline__ void store_pe_block(uint8_t* blk, uint32_t row_base, 
 template <int MODE>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
                                           const float* __restrict__ s_walpha, float& sigma, uint8_t* sAct,
-                                          uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint8_t* gmask) {
+                                          uint32_t row_base, uint32_t row_xor, uint8_t* grow, uint8_t* gmask, uint32_t (&mbits)[8]) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -157,10 +185,14 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
 #pragma unroll
   for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
   if (grow) {
-    uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
+    if (NERF_DEFER_STORES) {          // arena copy + mask words after the hand-over (flush_row_to_arena)
+      if (MODE != 2) mbits[c0 >> 5] = pos_bits32(pk);
+    } else {
+      uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-    if (MODE != 2) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
+      for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+      if (MODE != 2) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
+    }
   }
 }
 
@@ -169,17 +201,17 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
 template <int MODE>
 __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restrict__ s_walpha,
                                           float& sigma, uint8_t* sAct, uint32_t row_base, uint32_t row_xor, uint8_t* grow,
-                                          uint8_t* gmask) {
+                                          uint8_t* gmask, uint32_t (&mbits)[8]) {
   uint32_t va[32], vb[32];
   tmem_ld32(taddr, va);
 #pragma unroll
   for (int c = 0; c < 8; c += 2) {
     tmem_wait_ld();
     tmem_ld32(taddr + (c + 1) * 32, vb);
-    epi_chunk<MODE>(va, c * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
+    epi_chunk<MODE>(va, c * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask, mbits);
     tmem_wait_ld();
     if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
-    epi_chunk<MODE>(vb, (c + 1) * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask);
+    epi_chunk<MODE>(vb, (c + 1) * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask, mbits);
   }
 }
 
@@ -296,7 +328,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
               mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
               // both halves complete on the leader's barrier, which expects the bytes of the pair
               if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
-              tma_stage_cg2(smem + kOffW + slot * kHalfBytes, sched_n(li) == 256 ? &tm128 : &tm64,
+              tma_stage_cg2(smem + ring_slot_off(slot), sched_n(li) == 256 ? &tm128 : &tm64,
                             stage_row0 + (sched_start(li) + kb) * 256 + (int)rank * (sched_n(li) / 2), w_full_leader + slot * 8u);
             }
           }
@@ -322,7 +354,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
     // ===== MMA issuer (leader CTA) =====
     {                                   // the whole warp, converged: see umma_ss2_w
       uint32_t it = 0, itb = 0, lc = 0;
-      const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE), sW = smem_u32(smem + kOffW);
+      const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li, ++lc) {
           const int nkb = sched_nkb(li);
@@ -337,7 +369,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
           auto issue = [&](int tile, int kb, uint32_t slot) {
             const int ablk = a_block(kb);
             const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
-            const uint32_t b_base = sW + slot * kHalfBytes;
+            const uint32_t b_base = smem_u32(smem) + ring_slot_off(slot);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
               umma_ss2_w(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
@@ -448,8 +480,10 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
       uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 4 : nullptr;
       auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
       auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
-      store_pe_block(sPe, row_base, row_xor, pe, gblk(arena::kActPE));
+      constexpr bool kDefer = SAVE && NERF_DEFER_STORES;
+      store_pe_block(sPe, row_base, row_xor, pe, kDefer ? nullptr : gblk(arena::kActPE));
       signal_ready();
+      if (kDefer) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPE));      // from the registers, after the hand-over
 
       float sigma = 0.f;
       bool nvalid = false;
@@ -467,12 +501,22 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
         tc_fence_after();
         if (li < 9) {
           uint8_t* grow = gblk(li < 8 ? arena::kActH + 4 * li : arena::kActFeat);
-          if (li == 7) epi_layer<1>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
-          else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr);
-          else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li));
+          uint32_t mbits[8];
+          if (li == 7) epi_layer<1>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li), mbits);
+          else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr, mbits);
+          else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li), mbits);
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
-          if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, gblk(arena::kActPEDir));
+          if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, kDefer ? nullptr : gblk(arena::kActPEDir));
           signal_ready();
+          if (kDefer) {        // arena copy of this layer's output, its ReLU bit masks and (layer 5) PE(dir), off the critical path
+            flush_row_to_arena(sAct, row_base, row_xor, grow, 4);
+            if (li != 8) {
+              uint8_t* gm = gmsk(arena::kMaskH + li);
+#pragma unroll
+              for (int w = 0; w < 8; ++w) *reinterpret_cast<uint32_t*>(gm + w * arena::kMaskWordStride) = mbits[w];
+            }
+            if (li == 5) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPEDir));
+          }
         } else {
           float r0 = 0.f, r1 = 0.f, r2 = 0.f;
           epi_views<SAVE>(taddr, s_wrgb, r0, r1, r2, gblk(arena::kActHV), gmsk(arena::kMaskHV));

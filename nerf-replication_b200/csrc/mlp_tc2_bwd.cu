@@ -56,15 +56,36 @@ __device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, fl
   c = __cosf(ang);
 }
 
-// 16 packed words (32 columns) -> shared-memory A operand (swizzled) + this row of the gradient arena block
+// NERF_DEFER_STORES (default 0): experiment -- gradient-arena copy after the hand-over, re-read from shared memory; measured
+// slower (see mlp_tc2.cu).
+#ifndef NERF_DEFER_STORES
+#define NERF_DEFER_STORES 0
+#endif
+// 16 packed words (32 columns) -> shared-memory A operand (swizzled) [+ this row of the gradient arena block]
 __device__ __forceinline__ void put_chunk(const uint32_t (&pk)[16], int c0, uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint8_t* blk = sA + (c0 >> 6) * 16384;
   const int ch0 = (c0 & 63) >> 3;
 #pragma unroll
   for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-  uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
+  if (!NERF_DEFER_STORES) {
+    uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  }
+}
+// re-read this row's n_blocks x 128 bytes from the (swizzled) A operand and stream them to the arena blocks at grow
+__device__ __forceinline__ void flush_row_to_arena(const uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow, int n_blocks) {
+  if (!NERF_DEFER_STORES) return;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    if (b < n_blocks) {
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        const uint4 v = *reinterpret_cast<const uint4*>(sA + b * 16384 + row_base + (((uint32_t)ch ^ row_xor) << 4));
+        st_global_cs(grow + b * 16384 + ch * 1024, v.x, v.y, v.z, v.w);
+      }
+    }
+  }
 }
 
 // Epilogue of a masked step (F, L7..L1): 256 accumulator columns -> (+ d_sigma * w_alpha for F) -> bf16 -> AND
@@ -293,6 +314,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         }
       }
       signal_ready();
+      flush_row_to_arena(sA, row_base, row_xor, grow0 + (size_t)(FINE ? arena::kGradHV : arena::kGradZ + 28) * arena::kBlockBytes, kInitBlocks);
 
       for (int i = 0; i < kSteps; ++i, ++lc) {
         const int s = step_at(i);
@@ -361,6 +383,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           else if (s == S_F) epi_masked<true>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
           else epi_masked<false>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
           if (i + 1 < kSteps) signal_ready(); else tc_fence_before();
+          flush_row_to_arena(sA, row_base, row_xor, grow, 4);
         }
       }
     }
