@@ -2,8 +2,14 @@
 
 The reference gets this from a DataLoader driven by a sampler stack (src/datasets/make_dataset.py:37-71 building
 src/datasets/samplers.py:50-131 on torch's samplers).  Here the images never leave HBM, so all that is left of that
-stack is its stream of integers; ``ViewSchedule`` produces exactly that stream (checked against the reference's own
-sampler objects in tests/golden/loop_samplers.json) with no DataLoader, workers or collate behind it.
+stack is its stream of integers; ``ViewSchedule`` produces that stream with no DataLoader, workers or collate behind it.
+
+Exactness: the distributed path (``DistributedSampler`` re-seeded per epoch, train.py:60-61) and one pass of the
+iteration-based sampler are bit-equal to the reference's own sampler objects (tests/golden/loop_samplers.json).  The
+single-process shuffled path has the same distribution but NOT the same stream from the second epoch on: the reference's
+``IterationBasedBatchSampler`` loops ``while iteration <= num_iterations`` (samplers.py:60-72) and therefore starts one
+extra ``RandomSampler`` pass whenever ``ep_iter`` is a multiple of the pass length (lego.yaml: 500 = 5 x 100), and
+``DataLoader.__iter__`` draws a base seed per epoch -- both consume the global RNG, which this class does not emulate.
 """
 import torch
 
