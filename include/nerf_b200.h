@@ -215,6 +215,9 @@ int nerf_debug_tc_watchdog(unsigned int* out8);
  * out (host, may be NULL) receives the counters accumulated so far: 2 x 512 uint64, [0,512) forward kernel,
  * [512,1024) dgrad/wgrad kernels; within each, [b] = cycles warps spent waiting on barriers tagged b, [256+b] = waits. */
 int nerf_debug_waitprof(int on, unsigned long long* out);
+/* event trace of the diagnostic build -DNERF_TC_TRACE (`build.py --trace`): out[0] = number of records, out[1..n) =
+ * (clock64 << 16 | tag) records of CTA 0 since the last nerf_debug_waitprof(1, ...); all zero in any other build.  n <= 8192. */
+int nerf_debug_trace(unsigned long long* out, int n);
 
 #ifdef __cplusplus
 }

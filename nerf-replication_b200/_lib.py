@@ -65,6 +65,7 @@ SIGNATURES = {
     "nerf_eval_ssim": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
     "nerf_debug_tc_watchdog": (_I, [C.POINTER(C.c_uint)]),
     "nerf_debug_waitprof": (_I, [_I, C.POINTER(C.c_ulonglong)]),
+    "nerf_debug_trace": (_I, [C.POINTER(C.c_ulonglong), _I]),
 }
 
 # include/nerf_b200_probe.h: the bring-up probe battery, a separate library (not part of the product .so)

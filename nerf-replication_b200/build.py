@@ -59,6 +59,12 @@ def build_experiment(bits, verbose=False):
     return _build(OUT.replace(".so", "_exp%d.so" % bits), os.path.join(HERE, "build_exp%d" % bits), SOURCES, ["-DNERF_EXP=%d" % bits], verbose)
 
 
+def build_trace(verbose=False):
+    """Diagnostic flavour libnerf_b200_trace.so (-DNERF_TC_WAITPROF -DNERF_TC_TRACE): CTA 0 of the CTA-pair kernels logs
+    time-stamped events (profiles/trace_step.py)."""
+    return _build(OUT.replace(".so", "_trace.so"), os.path.join(HERE, "build_trace"), SOURCES, ["-DNERF_TC_WAITPROF", "-DNERF_TC_TRACE"], verbose)
+
+
 def build(force=False, verbose=False, waitprof=False):
     """waitprof=True builds the diagnostic flavour libnerf_b200_waitprof.so (-DNERF_TC_WAITPROF: every barrier wait of the
     CTA-pair kernels is timed); select it with NERF_B200_LIB=<path>.  The product library never carries that code."""
@@ -103,6 +109,9 @@ def _build(out, objdir, sources, extra, verbose):
 
 
 if __name__ == "__main__":
+    if "--trace" in sys.argv:
+        print(build_trace(verbose=True))
+        sys.exit(0)
     if "--exp" in sys.argv:
         print(build_experiment(int(sys.argv[sys.argv.index("--exp") + 1]), verbose=True))
         sys.exit(0)

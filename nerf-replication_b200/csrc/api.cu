@@ -65,6 +65,7 @@ extern "C" int nerf_create(const NerfConfig* cfg, int device, NerfEngine** out) 
   h->cfg = *cfg;
   h->device = device;
   h->num_sms = prop.multiProcessorCount;
+  if (const char* v = getenv("NERF_B200_WREPLICAS")) h->w_replicas = std::max(1, std::min(74, atoi(v)));
   *out = h;
   return NERF_OK;
 }
@@ -78,6 +79,7 @@ extern "C" int nerf_destroy(NerfEngine* h) {
   for (auto& b : h->banks) { if (b.images) cudaFree(b.images); if (b.poses) cudaFree(b.poses); }
   if (h->wpack) cudaFree(h->wpack);
   if (h->wpack_bwd) cudaFree(h->wpack_bwd);
+  if (h->wrep) cudaFree(h->wrep);
   for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
@@ -114,7 +116,18 @@ static int post(NerfEngine* h, const char* what) {
 
 // The packed bf16 images are written on the caller's stream; the host-buffer render path runs on the engine's own
 // streams and must not read them before the (re)pack has finished.
+// copies of the forward stage images for the CTA pairs to spread over (engine.h: wrep)
+static int replicate_weights(NerfEngine* h, cudaStream_t st) {
+  if (h->w_replicas <= 1) return NERF_OK;
+  const size_t S = tc_wpack_bias_offset();      // the stage images of both nets
+  if (!h->wrep) NERF_CUDA_TRY(h, cudaMalloc(&h->wrep, S * h->w_replicas));
+  for (int r = 0; r < h->w_replicas; ++r)
+    NERF_CUDA_TRY(h, cudaMemcpyAsync(reinterpret_cast<uint8_t*>(h->wrep) + (size_t)r * S, h->wpack, S, cudaMemcpyDeviceToDevice, st));
+  return NERF_OK;
+}
+
 static int record_pack(NerfEngine* h, cudaStream_t st) {
+  if (int rc = replicate_weights(h, st)) return rc;
   if (!h->pack_ev) NERF_CUDA_TRY(h, cudaEventCreateWithFlags(&h->pack_ev, cudaEventDisableTiming));
   NERF_CUDA_TRY(h, cudaEventRecord(h->pack_ev, st));
   return NERF_OK;
@@ -728,6 +741,16 @@ extern "C" int nerf_clip_adam(NerfEngine* h, float* flat_param, const float* fla
 // Wait profile of the CTA-pair kernels (tc_common.cuh waitprof_add).  on != 0: (re)start with zeroed counters; on == 0: stop.
 // out (may be NULL): 2 x 512 uint64 read before the state change -- [0,512) forward TU, [512,1024) backward TU; each
 // [b] = cycles in slow-path waits of tag bucket b = (tag >> 4) & 255, [256 + b] = number of such waits.
+static unsigned long long* g_waitprof_buf = nullptr;
+// Event trace of the diagnostic build -DNERF_TC_TRACE (tc_common.cuh trace_event): out[0] = number of records, out[1..n) =
+// records (clock64 << 16 | tag) of CTA 0 since the last nerf_debug_waitprof(1, ...).  Zeros in any other build.
+extern "C" int nerf_debug_trace(unsigned long long* out, int n) {
+  if (!out || n < 1 || n > 8192) return NERF_E_INVALID;
+  cudaDeviceSynchronize();
+  if (!g_waitprof_buf) { memset(out, 0, (size_t)n * sizeof(unsigned long long)); return NERF_OK; }
+  return cudaMemcpy(out, g_waitprof_buf + 1024, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess ? NERF_OK : NERF_E_CUDA;
+}
+
 extern "C" int nerf_debug_waitprof(int on, unsigned long long* out) {
   static unsigned long long* buf = nullptr;
   cudaDeviceSynchronize();
@@ -736,8 +759,9 @@ extern "C" int nerf_debug_waitprof(int on, unsigned long long* out) {
     else memset(out, 0, 1024 * sizeof(unsigned long long));
   }
   if (on) {
-    if (!buf && cudaMalloc(&buf, 1024 * sizeof(unsigned long long)) != cudaSuccess) return NERF_E_CUDA;
-    cudaMemset(buf, 0, 1024 * sizeof(unsigned long long));
+    if (!buf && cudaMalloc(&buf, (1024 + 8192) * sizeof(unsigned long long)) != cudaSuccess) return NERF_E_CUDA;
+    cudaMemset(buf, 0, (1024 + 8192) * sizeof(unsigned long long));
+    g_waitprof_buf = buf;
     nerf::tc2_set_debug_sink_waitprof(buf);
     nerf::tc2b_set_debug_sink_waitprof(buf + 512);
   } else {

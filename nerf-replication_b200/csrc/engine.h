@@ -18,6 +18,10 @@ struct NerfEngine {
   __nv_bfloat16* wpack = nullptr;  // packed bf16 weight images for the tcgen05 kernels
   size_t wpack_bytes = 0;
   __nv_bfloat16* wpack_bwd = nullptr;   // transposed stage images for the dgrad chain (mlp_tc2_bwd.cu)
+  // Replicas of the forward stage images (NERF_B200_WREPLICAS = R > 1): CTA pair p streams replica p % R, so that the 74
+  // pairs, which walk the layers in lock step, do not all pull the same 256 L2 lines of the current stage at the same time
+  __nv_bfloat16* wrep = nullptr;
+  int w_replicas = 1;
   // tensor maps (CUtensorMap, 128 bytes each) over the packed stage images for the 2-SM TMA weight loads of mlp_tc2.cu:
   // boxes of 128 / 64 rows; encoded for tmap_base == wpack
   alignas(64) unsigned char tmaps[2][128] = {};

@@ -261,7 +261,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
 __device__ __forceinline__ void tma_stage_cg2(void* smem_dst, const CUtensorMap* tmap, int row0, uint32_t mbar_cluster_addr) {
   asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                    smem_u32(smem_dst)),
-               "l"(tmap), "r"(0), "r"(row0), "r"(mbar_cluster_addr)
+               "l"(tmap), "r"(0), "r"(row0 >> 2), "r"(mbar_cluster_addr)      // the maps see the image as rows of 512 bytes (4 image rows)
                : "memory");
 }
 
@@ -271,7 +271,7 @@ __device__ __forceinline__ void tma_stage_cg2(void* smem_dst, const CUtensorMap*
 // blocks cost 40 % of the kernel: their shared-memory reads compete with the MMA operand fetch.)
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64, int stage_row0,
+mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64, int stage_row0, int n_rep,
                        RowSrc src, float4* __restrict__ raw, const uint8_t* __restrict__ wbias, const float* __restrict__ P, int64_t M, int64_t n_pair,
                        uint8_t* __restrict__ act_arena) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -279,13 +279,15 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
     M = min((int64_t)__ldg(src.row_count), M);
     n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
   }
-  constexpr int kReps = SAVE ? 2 : 1;            // weight passes per layer (training: once per tile, see the issuer)
+  constexpr bool kPerTile = SAVE && !(NERF_EXP & 32);   // NERF_EXP bit 5: the saving forward in the render (shared-stage) order
+  constexpr int kReps = kPerTile ? 2 : 1;            // weight passes per layer (training: once per tile, see the issuer)
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
   float* s_wrgb = s_walpha + 256;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = cluster_ctarank();
   const int64_t pair0 = blockIdx.x >> 1, pair_stride = gridDim.x >> 1;
+  stage_row0 += (int)(pair0 % n_rep) * (2 * kNumStages * 256);              // this pair's replica of the stage images
 
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA12, smem_u32(smem));   // swizzle-128B needs 1024B alignment
   if (tid == 0) {
@@ -310,7 +312,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
   if (warp == 0) {
     // ===== weight producer (both CTAs): my half of every stage =====
     if (lane == 0) {
-      uint32_t it = 0, itb = 0;
+      uint32_t it = 0, itb = 0, tn_p = 0;
       const uint32_t w_full_leader = mapa_u32(smem_u32(&sb.w_full[0]), 0);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li) {
@@ -326,6 +328,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
             for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
               mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
+              trace_event(0x3000u | (rep << 8) | (li << 4) | (4u + kb), 1024, tn_p, 3000, 5000);
               // both halves complete on the leader's barrier, which expects the bytes of the pair
               if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
               tma_stage_cg2(smem + ring_slot_off(slot), sched_n(li) == 256 ? &tm128 : &tm64,
@@ -353,7 +356,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA) =====
     {                                   // the whole warp, converged: see umma_ss2_w
-      uint32_t it = 0, itb = 0, lc = 0;
+      uint32_t it = 0, itb = 0, lc = 0, tn = 0;
       const uint32_t sA = smem_u32(smem + kOffA), sPE = smem_u32(smem + kOffPE);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li, ++lc) {
@@ -376,18 +379,20 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
                        make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, 1u);
             }
           };
-          if (SAVE) {
+          if (kPerTile) {
             // Training forward: one tile's whole layer, then the other's -- the layer's weights are streamed twice (L2
             // hits) so that tile Y's MMAs run under tile X's long (arena-storing) epilogue.
 #pragma unroll
             for (int tile = 0; tile < 2; ++tile) {
               mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
               tc_fence_after();
+              if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | 1u, 1024, tn, 0, 3000);
               {
                 const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
                 ++itb;
                 mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
                 tc_fence_after();
+                if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | 2u, 1024, tn, 0, 3000);
                 issue_bias(tile, bslot);
                 umma_commit2_w(&sb.b_empty[bslot], 0x3);
               }
@@ -395,10 +400,12 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
                 const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
                 if (!(NERF_EXP & 2)) mbar_wait(&sb.w_full[slot], par, 0x20 + slot);
                 tc_fence_after();
+                if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | (4u + kb), 1024, tn, 0, 3000);
                 issue(tile, kb, slot);
                 umma_commit2_w(&sb.w_empty[slot], 0x3);
               }
               umma_commit2_w(&sb.acc_full[tile], 0x3);
+              if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | 3u, 1024, tn, 0, 3000);
             }
           } else {
             // Render: every weight stage feeds both tiles before it is released (half the weight traffic of the per-tile
@@ -455,7 +462,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
-    uint32_t lc = 0;
+    uint32_t lc = 0, tn_e = 0;
     // this row of pair super-tile st_: validity, global row (through the compacted row list when rows are skipped), point, view direction
     auto row_setup = [&](int64_t st_, bool& valid_, int64_t& g_, float (&p_)[3], float (&vd_)[3]) {
       const int64_t gl = st_ * kRowsPerPair + (int64_t)rank * kRowsPerCta + tile * kTile + row;
@@ -499,6 +506,8 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
         }
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
+        const bool tr = SAVE && q == 0 && lane == 0;
+        if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 1u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
         if (li < 9) {
           uint8_t* grow = gblk(li < 8 ? arena::kActH + 4 * li : arena::kActFeat);
           uint32_t mbits[8];
@@ -507,7 +516,9 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
           else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li), mbits);
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
           if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, kDefer ? nullptr : gblk(arena::kActPEDir));
+          if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 2u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
           signal_ready();
+          if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 3u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
           if (kDefer) {        // arena copy of this layer's output, its ReLU bit masks and (layer 5) PE(dir), off the critical path
             flush_row_to_arena(sAct, row_base, row_xor, grow, 4);
             if (li != 8) {
@@ -560,28 +571,34 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
   static_assert(sizeof(CUtensorMap) == sizeof(h->tmaps[0]), "CUtensorMap size");
   CUtensorMap& tm128 = *reinterpret_cast<CUtensorMap*>(h->tmaps[0]);
   CUtensorMap& tm64 = *reinterpret_cast<CUtensorMap*>(h->tmaps[1]);
-  if (h->tmap_base != h->wpack) {
+  const int n_rep = (h->w_replicas > 1 && h->wrep) ? h->w_replicas : 1;
+  const void* stage_base = n_rep > 1 ? (const void*)h->wrep : (const void*)h->wpack;
+  if (h->tmap_base != stage_base) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
       return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled not available");
-    const cuuint64_t gdim[2] = {64, (cuuint64_t)2 * kNumStages * 256}, gstride[1] = {128};
+    // A CTA's half of a stage is one contiguous run of 16 KB (8 KB for the view layer), so any 2-D factorisation of it copies
+    // the same bytes: the maps use rows of 512 bytes -- 32 (16) row requests per stage instead of 128 (64) rows of 128 bytes;
+    // in the per-tile (training) order a stage feeds only 512 clk of MMAs and the TMA unit's per-row request rate was what
+    // the issuer waited for.
+    const cuuint64_t gdim[2] = {256, (cuuint64_t)n_rep * 2 * kNumStages * 256 / 4}, gstride[1] = {512};
     const cuuint32_t estr[2] = {1, 1};
     for (int v = 0; v < 2; ++v) {
-      const cuuint32_t box[2] = {64, v == 0 ? 128u : 64u};
-      CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &tm128 : &tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)h->wpack, gdim, gstride, box, estr,
+      const cuuint32_t box[2] = {256, v == 0 ? 32u : 16u};
+      CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &tm128 : &tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(stage_base), gdim, gstride, box, estr,
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       if (r != CUDA_SUCCESS) return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled failed");
     }
-    h->tmap_base = h->wpack;
+    h->tmap_base = stage_base;
   }
   const int stage_row0 = (net == NERF_NET_FINE ? 1 : 0) * kNumStages * 256;
   const uint8_t* wb = reinterpret_cast<const uint8_t*>(h->wpack) + tc_wpack_bias_offset() + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumSched * kBiasSlabBytes;
-  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, act_arena);
-  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, nullptr);
+  if (act_arena) mlp_tc2_forward_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, n_rep, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, act_arena);
+  else mlp_tc2_forward_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(tm128, tm64, stage_row0, n_rep, src, reinterpret_cast<float4*>(raw), wb, P, M, n_pair, nullptr);
   h->launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return h->fail(NERF_E_CUDA, std::string("mlp_tc2_forward launch: ") + cudaGetErrorString(e));

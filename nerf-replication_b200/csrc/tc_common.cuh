@@ -33,6 +33,21 @@ __device__ __forceinline__ void waitprof_add(uint32_t tag, long long t0) {
 __device__ __forceinline__ long long waitprof_now() { return 0; }
 __device__ __forceinline__ void waitprof_add(uint32_t, long long) {}
 #endif
+// event trace (diagnostic build -DNERF_TC_TRACE, read with nerf_debug_trace): CTA 0 appends (clock64 << 16 | tag) records
+// behind the wait-profile counters; `base` = offset of the trace area relative to this translation unit's counter block
+#ifdef NERF_TC_TRACE
+// plain stores into a per-role region [lo, hi) of the trace area (no atomics: a returning atomic costs ~800 clk of the
+// thread being traced); `n` is the role's own running count (a register)
+__device__ __forceinline__ void trace_event(uint32_t tag, int base, uint32_t& n, uint32_t lo, uint32_t hi) {
+  unsigned long long* p = g_tc_waitprof;
+  if (p != nullptr && blockIdx.x == 0 && lo + n < hi) {
+    p[base + 1 + lo + n] = ((unsigned long long)clock64() << 16) | tag;
+    ++n;
+  }
+}
+#else
+__device__ __forceinline__ void trace_event(uint32_t, int, uint32_t&, uint32_t, uint32_t) {}
+#endif
 
 // ---- mbarrier ---------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
