@@ -36,7 +36,8 @@ __global__ void clip_adam_kernel(float4* __restrict__ p, const float4* __restric
 __global__ void __launch_bounds__(256) clip_adam_pack_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m,
                                                              float4* __restrict__ v, int64_t n4, float beta1, float beta2, float step_size,
                                                              float inv_bc2_sqrt, float eps, float clip, __nv_bfloat16* __restrict__ wpack,
-                                                             uint8_t* __restrict__ slabs, __nv_bfloat16* __restrict__ wpack_bwd) {
+                                                             uint8_t* __restrict__ slabs, __nv_bfloat16* __restrict__ wpack_bwd,
+                                                             __nv_bfloat16* __restrict__ rep, int n_rep) {
   const int64_t tid0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = tid0; i < n4; i += stride) {
     float4 pp = p[i], gg = __ldg(g + i), mm = m[i], vv = v[i];
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(256) clip_adam_pack_kernel(float4* __restrict_
   const float* flat = reinterpret_cast<const float*>(p);
   const int64_t total = fwdpack::kWeightChunks + bw::kDgradChunks + fwdpack::kBiasRows;
   for (int64_t e = tid0; e < total; e += stride) {
-    if (e < fwdpack::kWeightChunks) fwdpack::pack_weight_chunk(e, flat, wpack);
+    if (e < fwdpack::kWeightChunks) fwdpack::pack_weight_chunk(e, flat, wpack, rep, n_rep);
     else if (e < fwdpack::kWeightChunks + bw::kDgradChunks) bw::pack_dgrad_chunk(e - fwdpack::kWeightChunks, flat, wpack_bwd);
     else fwdpack::pack_bias_row((int)(e - fwdpack::kWeightChunks - bw::kDgradChunks), flat, slabs);
   }
@@ -83,7 +84,9 @@ int launch_clip_adam_pack(NerfEngine* h, float* p, const float* g, float* m, flo
   float4* m4 = reinterpret_cast<float4*>(m); float4* v4 = reinterpret_cast<float4*>(v);
   int64_t n4 = n / 4;
   float step_size = sc.step_size, inv = sc.inv_bc2_sqrt;
-  void* args[] = {&p4, &g4, &m4, &v4, &n4, &b1, &b2, &step_size, &inv, &eps, &clip, &wpack, &slabs, &wpack_bwd};
+  __nv_bfloat16* rep = h->wrep;
+  int n_rep = h->wrep ? h->w_replicas : 0;
+  void* args[] = {&p4, &g4, &m4, &v4, &n4, &b1, &b2, &step_size, &inv, &eps, &clip, &wpack, &slabs, &wpack_bwd, &rep, &n_rep};
   const int grid = h->num_sms * std::min(bps, 8);     // every CTA resident: the grid barrier needs it
   prefer_max_shared(reinterpret_cast<const void*>(clip_adam_pack_kernel), h->device);
   cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(clip_adam_pack_kernel), dim3(grid), dim3(256), args, 0, st);

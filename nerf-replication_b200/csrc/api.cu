@@ -116,18 +116,7 @@ static int post(NerfEngine* h, const char* what) {
 
 // The packed bf16 images are written on the caller's stream; the host-buffer render path runs on the engine's own
 // streams and must not read them before the (re)pack has finished.
-// copies of the forward stage images for the CTA pairs to spread over (engine.h: wrep)
-static int replicate_weights(NerfEngine* h, cudaStream_t st) {
-  if (h->w_replicas <= 1) return NERF_OK;
-  const size_t S = tc_wpack_bias_offset();      // the stage images of both nets
-  if (!h->wrep) NERF_CUDA_TRY(h, cudaMalloc(&h->wrep, S * h->w_replicas));
-  for (int r = 0; r < h->w_replicas; ++r)
-    NERF_CUDA_TRY(h, cudaMemcpyAsync(reinterpret_cast<uint8_t*>(h->wrep) + (size_t)r * S, h->wpack, S, cudaMemcpyDeviceToDevice, st));
-  return NERF_OK;
-}
-
 static int record_pack(NerfEngine* h, cudaStream_t st) {
-  if (int rc = replicate_weights(h, st)) return rc;
   if (!h->pack_ev) NERF_CUDA_TRY(h, cudaEventCreateWithFlags(&h->pack_ev, cudaEventDisableTiming));
   NERF_CUDA_TRY(h, cudaEventRecord(h->pack_ev, st));
   return NERF_OK;
@@ -144,6 +133,7 @@ extern "C" int nerf_set_params(NerfEngine* h, const float* flat, void* stream) {
     NERF_CUDA_TRY(h, cudaMemsetAsync(h->wpack, 0, h->wpack_bytes, (cudaStream_t)stream));
   }
   if (!h->wpack_bwd) NERF_CUDA_TRY(h, cudaMalloc(&h->wpack_bwd, tc_bwd_wpack_bytes()));
+  if (h->w_replicas > 1 && !h->wrep) NERF_CUDA_TRY(h, cudaMalloc(&h->wrep, tc_wpack_bias_offset() * h->w_replicas));   // replicas of the stage images
   tc_pack_all(h, flat, h->wpack, h->wpack_bwd, (cudaStream_t)stream);
   h->params_set = true;
   if (int rc = record_pack(h, (cudaStream_t)stream)) return rc;

@@ -36,7 +36,9 @@ inline size_t wpack_bias_offset() { return (size_t)2 * kNumStages * kStageBytes;
 inline size_t wpack_bytes() { return wpack_bias_offset() + (size_t)2 * kNumSched * kBiasSlabBytes; }
 
 constexpr int64_t kWeightChunks = (int64_t)2 * kNumStages * 256 * 8;
-__device__ __forceinline__ void pack_weight_chunk(int64_t e, const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack) {
+// rep / n_rep: optional replicas of the stage images (engine.h wrep): the chunk is also written to each of them
+__device__ __forceinline__ void pack_weight_chunk(int64_t e, const float* __restrict__ flat, __nv_bfloat16* __restrict__ wpack,
+                                                  __nv_bfloat16* __restrict__ rep = nullptr, int n_rep = 0) {
   {
     const int kc = (int)(e & 7), n = (int)((e >> 3) & 255);
     const int s = (int)((e >> 11) % kNumStages), net = (int)((e >> 11) / kNumStages);
@@ -64,8 +66,10 @@ __device__ __forceinline__ void pack_weight_chunk(int64_t e, const float* __rest
       const __nv_bfloat162 b2 = __floats2bfloat162_rn(w2[0], w2[1]);
       pk[j] = *reinterpret_cast<const uint32_t*>(&b2);
     }
-    uint8_t* dst = reinterpret_cast<uint8_t*>(wpack) + ((int64_t)net * kNumStages + s) * kStageBytes + sw128_offset(n, kc);
-    *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    const int64_t off = ((int64_t)net * kNumStages + s) * kStageBytes + sw128_offset(n, kc);
+    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(wpack) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    for (int r = 0; r < n_rep; ++r)
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(rep) + (int64_t)r * (2 * kNumStages * kStageBytes) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
   }
 }
 
