@@ -258,10 +258,14 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
 // [rows x 64] bf16 matrix) that completes on an mbarrier of EITHER CTA of the pair (.cta_group::2): both halves signal the
 // leader's w_full directly.  A plain cp.async.bulk can only signal a barrier of its destination CTA, so the peer's arrival
 // had to be relayed by a forwarder warp (peer barrier -> poll -> remote arrive): that hop sat on the ring's round trip.
+// The maps see the packed image as rows of (128 << kTmaRowShift) bytes.  A CTA's half of a stage is one contiguous run, so
+// any 2-D factorisation copies the same bytes.  Measured A/B on the C2 render (profiles/exp_train_r2.md): 128-byte rows
+// 154.2-154.4 ms, 512-byte rows 154.9-155.5 ms, training step unchanged -> 128-byte rows.
+constexpr int kTmaRowShift = 0;
 __device__ __forceinline__ void tma_stage_cg2(void* smem_dst, const CUtensorMap* tmap, int row0, uint32_t mbar_cluster_addr) {
   asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                    smem_u32(smem_dst)),
-               "l"(tmap), "r"(0), "r"(row0 >> 2), "r"(mbar_cluster_addr)      // the maps see the image as rows of 512 bytes (4 image rows)
+               "l"(tmap), "r"(0), "r"(row0 >> kTmaRowShift), "r"(mbar_cluster_addr)
                : "memory");
 }
 
@@ -580,14 +584,11 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
       return h->fail(NERF_E_CUDA, "mlp_tc2: cuTensorMapEncodeTiled not available");
-    // A CTA's half of a stage is one contiguous run of 16 KB (8 KB for the view layer), so any 2-D factorisation of it copies
-    // the same bytes: the maps use rows of 512 bytes -- 32 (16) row requests per stage instead of 128 (64) rows of 128 bytes;
-    // in the per-tile (training) order a stage feeds only 512 clk of MMAs and the TMA unit's per-row request rate was what
-    // the issuer waited for.
-    const cuuint64_t gdim[2] = {256, (cuuint64_t)n_rep * 2 * kNumStages * 256 / 4}, gstride[1] = {512};
+    // rows of (128 << kTmaRowShift) bytes (see tma_stage_cg2); box = a CTA's half of a stage: 16 KB (8 KB for the view layer)
+    const cuuint64_t gdim[2] = {64u << kTmaRowShift, ((cuuint64_t)n_rep * 2 * kNumStages * 256) >> kTmaRowShift}, gstride[1] = {128u << kTmaRowShift};
     const cuuint32_t estr[2] = {1, 1};
     for (int v = 0; v < 2; ++v) {
-      const cuuint32_t box[2] = {256, v == 0 ? 32u : 16u};
+      const cuuint32_t box[2] = {64u << kTmaRowShift, (v == 0 ? 128u : 64u) >> kTmaRowShift};
       CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &tm128 : &tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(stage_base), gdim, gstride, box, estr,
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
