@@ -199,6 +199,21 @@ int nerf_bank_train_step(NerfEngine* h, int bank, int view, int mode, const int6
  * (numpy uint8 arithmetic wraps, :24-26) -> mse8 = sq8/n_elems, psnr = 100 if mse8 < 1e-10 else 10 log10(255^2/mse8). */
 int nerf_eval_image(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int64_t n_elems, double* sse_out,
                     unsigned long long* sq8_out, void* stream);
+/* nerf_eval_image without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, same kernel, same grid and therefore the same bits as nerf_eval_image; the scratch of the grid reduction
+ * (per-block partial sums + a counter) is a file-scope device array of NERF_EVAL_STATIC_SCRATCH_BYTES that every GPU loading
+ * the library holds until exit, instead of the engine's cudaMalloc'ed workspace.  The call performs no cudaMalloc / cudaFree
+ * (the first call on a device looks the array's address up with cudaGetSymbolAddress: make that call outside a capture).
+ * Limits: n_elems <= NERF_EVAL_STATIC_MAX_ELEMS and a grid of at most NERF_EVAL_STATIC_MAX_BLOCKS blocks (4 per SM: devices
+ * up to 256 SMs); beyond either the call returns NERF_E_INVALID and nerf_last_error() says which.  All calls on a device
+ * share the array (it keeps the last call's contents; the counter is cleared on `stream` before each launch): calls that
+ * overlap on the GPU -- different streams, or different engines on one device -- race; serialise them. */
+#define NERF_EVAL_STATIC_MAX_ELEMS (1 << 27)      /* floats per image: 134 217 728 (e.g. 6688 x 6688 x 3)      */
+#define NERF_EVAL_STATIC_MAX_BLOCKS 1024
+#define NERF_EVAL_STATIC_SCRATCH_BYTES 16640      /* 1024 x (8 + 8) B of partials + a 256 B counter line      */
+int nerf_eval_image_static(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int64_t n_elems, double* sse_out,
+                           unsigned long long* sq8_out, void* stream);
 /* ssim_metric, src/evaluators/nerf.py:52-77 = skimage.metrics.structural_similarity(uint8 pred, uint8 gt, win_size,
  * channel_axis=2) on x8 = trunc(clip(x,0,1)*255) of [H,W,3] images: *ssim_sum_out (device double) = sum of the SSIM map
  * over its border-cropped (H-win+1)x(W-win+1) region and the 3 channels; ssim = sum / (3 (H-win+1)(W-win+1)). */

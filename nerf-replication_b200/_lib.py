@@ -62,6 +62,7 @@ SIGNATURES = {
     "nerf_bank_permutation_host": (_I, [C.c_uint64, C.c_uint64, _L, _L, _P]),
     "nerf_bank_train_step": (_I, [_P, _I, _I, _I, _P, _L, C.c_uint64, _L, _P, _P, _F, _P, _P, _P, _P]),
     "nerf_eval_image": (_I, [_P, _P, _P, _L, _P, _P, _P]),
+    "nerf_eval_image_static": (_I, [_P, _P, _P, _L, _P, _P, _P]),
     "nerf_eval_ssim": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
     "nerf_debug_tc_watchdog": (_I, [C.POINTER(C.c_uint)]),
     "nerf_debug_waitprof": (_I, [_I, C.POINTER(C.c_ulonglong)]),

@@ -10,6 +10,7 @@
 //                uint8-quantised PSNR sum *with numpy's uint8 wrap-around* ((a-b) mod 256, squared mod 256), as
 //                exact integers.
 // Both are HBM-bound gather / streaming kernels.
+#include <mutex>
 #include <vector>
 #include "engine.h"
 
@@ -326,6 +327,63 @@ extern "C" int nerf_eval_image(NerfEngine* h, const float* rgb_pred, const float
   h->launches++;
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? NERF_OK : h->fail(NERF_E_CUDA, std::string("nerf_eval_image: ") + cudaGetErrorString(e));
+}
+
+// ---- allocation-free variant of nerf_eval_image ------------------------------------------------------
+// (no counterpart in the reference; for callers that cannot call cudaMalloc: graph capture, serving loops.)  The per-block
+// partials and the "blocks done" counter of the grid fold live in a file-scope device array instead of the engine's
+// workspace (h->buf = cudaMalloc on first use).  Every GPU that loads the library holds these NERF_EVAL_STATIC_SCRATCH_BYTES
+// until exit; every call on a device shares them, so two calls that overlap on the GPU race.
+struct EvalStaticScratch {
+  double part_sse[NERF_EVAL_STATIC_MAX_BLOCKS];
+  unsigned long long part_sq8[NERF_EVAL_STATIC_MAX_BLOCKS];
+  unsigned int done;
+  unsigned int pad[63];
+};
+static_assert(sizeof(EvalStaticScratch) == NERF_EVAL_STATIC_SCRATCH_BYTES, "header constant");
+static __device__ __align__(256) unsigned char g_eval_static_scratch[sizeof(EvalStaticScratch)];
+
+// In host code `g_eval_static_scratch` is only the symbol's host-side stand-in: the device address is looked up once per
+// device, with that device current, and that pointer is what the kernel gets.
+static int eval_static_scratch(NerfEngine* h, EvalStaticScratch** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static EvalStaticScratch* ptr[kMaxDev] = {};
+  if (h->device < 0 || h->device >= kMaxDev) return h->fail(NERF_E_INVALID, "nerf_eval_image_static: device index out of range");
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[h->device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_eval_static_scratch);
+    if (e != cudaSuccess || !p) return h->fail(NERF_E_CUDA, std::string("nerf_eval_image_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    ptr[h->device] = static_cast<EvalStaticScratch*>(p);
+  }
+  *out = ptr[h->device];
+  return NERF_OK;
+}
+
+extern "C" int nerf_eval_image_static(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int64_t n_elems, double* sse_out,
+                                      unsigned long long* sq8_out, void* stream) {
+  if (!h) return NERF_E_INVALID;
+  if (!rgb_pred || !rgb_gt || n_elems <= 0 || !sse_out || !sq8_out) return h->fail(NERF_E_INVALID, "nerf_eval_image_static: bad argument");
+  if (n_elems > (int64_t)NERF_EVAL_STATIC_MAX_ELEMS)
+    return h->fail(NERF_E_INVALID, "nerf_eval_image_static: n_elems " + std::to_string((long long)n_elems) + " exceeds NERF_EVAL_STATIC_MAX_ELEMS (" +
+                                       std::to_string((long long)NERF_EVAL_STATIC_MAX_ELEMS) + "); use nerf_eval_image");
+  // the same grid as nerf_eval_image => the same per-thread order of terms and the same fold => the same bits
+  const int64_t blocks = std::min<int64_t>((n_elems + kEvalThreads - 1) / kEvalThreads, (int64_t)h->num_sms * 4);
+  if (blocks > NERF_EVAL_STATIC_MAX_BLOCKS)
+    return h->fail(NERF_E_INVALID, "nerf_eval_image_static: the grid of this device (" + std::to_string((long long)blocks) +
+                                       " blocks) exceeds the static scratch (NERF_EVAL_STATIC_MAX_BLOCKS); use nerf_eval_image");
+  EvalStaticScratch* s = nullptr;
+  if (int rc = eval_static_scratch(h, &s)) return rc;
+  cudaSetDevice(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the last call's contents: the counter must start at zero (the partials are overwritten before they are read)
+  NERF_CUDA_TRY(h, cudaMemsetAsync(&s->done, 0, sizeof(unsigned int), st));
+  eval_image_kernel<<<(int)blocks, kEvalThreads, 0, st>>>(rgb_pred, rgb_gt, n_elems, s->part_sse, s->part_sq8, &s->done, sse_out, sq8_out);
+  h->launches++;
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? NERF_OK : h->fail(NERF_E_CUDA, std::string("nerf_eval_image_static: ") + cudaGetErrorString(e));
 }
 
 extern "C" int nerf_eval_ssim(NerfEngine* h, const float* rgb_pred, const float* rgb_gt, int H, int W, int win_size, double* ssim_sum_out,

@@ -346,6 +346,19 @@ class Engine:
                                              rgb_pred.numel(), sse.data_ptr(), sq8.data_ptr(), self._stream()))
         return sse, sq8
 
+    def eval_image_static(self, rgb_pred, rgb_gt, sse=None, sq8=None):
+        """nerf_eval_image_static: the same sums as eval_image, with the reduction scratch in a static device array (no
+        cudaMalloc in the call; no counterpart in the reference).  Pass preallocated `sse` (float64 []) and `sq8` (int64 [])
+        device tensors to keep this wrapper allocation-free as well."""
+        if rgb_pred.numel() != rgb_gt.numel():
+            raise EngineError("eval_image_static: rgb_pred and rgb_gt differ in size")
+        dev = "cuda:%d" % self.device
+        sse = torch.empty((), dtype=torch.float64, device=dev) if sse is None else sse
+        sq8 = torch.empty((), dtype=torch.int64, device=dev) if sq8 is None else sq8
+        self._check(self.lib.nerf_eval_image_static(self.h, self._p(rgb_pred, name="rgb_pred"), self._p(rgb_gt, name="rgb_gt"),
+                                                    rgb_pred.numel(), sse.data_ptr(), sq8.data_ptr(), self._stream()))
+        return sse, sq8
+
     def eval_ssim(self, rgb_pred, rgb_gt, H, W, win_size=7):
         """-> device float64 []: mean SSIM as src/evaluators/nerf.py:71-77 computes it (see nerf_eval_ssim)."""
         if rgb_pred.numel() != H * W * 3 or rgb_gt.numel() != H * W * 3:
