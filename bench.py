@@ -58,10 +58,11 @@ def measured_hbm():
     return 6500.0, "fallback"
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one launch (the fine-net launch of each class), from the committed
-# ncu --set full captures: profiles/mlp_r1j_metrics.txt (render) and profiles/train_r1d_metrics.txt (training step)
-NCU_TRAFFIC_BYTES = {"render": {"fwd": 56.38e6 + 145.70e6},
-                     "train": {"fwd": 0.0021e9 + 1.0045e9, "dgrad": 0.0596e9 + 0.9499e9, "wgrad": 1.9247e9 + 0.0039e9}}
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch (the fine-net launch of each class), from the committed round-2
+# ncu captures: profiles/stages_render_r2z_metrics.txt (launch list with DRAM bytes; fine-net launches 54.1 MB read + 145.3 MB
+# written) and profiles/train_r2z_metrics.txt (ncu --set full of the training step's kernels)
+NCU_TRAFFIC_BYTES = {"render": {"fwd": 54.1e6 + 145.3e6},
+                     "train": {"fwd": 0.0022e9 + 1.0055e9, "dgrad": 0.0628e9 + 0.9509e9, "wgrad": 1.9327e9 + 0.0056e9}}
 
 
 def measured_peaks():
