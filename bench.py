@@ -63,6 +63,10 @@ def measured_hbm():
 # written) and profiles/train_r2z_metrics.txt (ncu --set full of the training step's kernels)
 NCU_TRAFFIC_BYTES = {"render": {"fwd": 54.1e6 + 145.3e6},
                      "train": {"fwd": 0.0022e9 + 1.0055e9, "dgrad": 0.0628e9 + 0.9509e9, "wgrad": 1.9327e9 + 0.0056e9}}
+# DRAM bytes (read + written) of ALL eight MLP launches of one 1024-ray step in the same capture (forward coarse/fine, dgrad
+# fine/coarse, wgrad + heads fine/coarse): 2.721 GB read + 2.475 GB written.  The activation / gradient arenas scale with the
+# ray count and the 2.5 MB of packed weights do not matter, so other batch sizes are scaled linearly.
+NCU_TRAIN_STEP_DRAM_BYTES_1024 = 2.7211e9 + 2.4751e9
 
 
 def measured_peaks():
@@ -553,6 +557,12 @@ def train_record(args, eng, net0, cfg, rank, world, dev, n_rays, timed, barrier,
            "step_tflops_per_gpu": flop_step / (ms_step / 1e3) / 1e12, "frac_of_sustained": flop_step / (ms_step / 1e3) / 1e12 / peak_sus,
            "gpu_launches_per_step": launches_per_step, "cuda_graph": not args.no_graph,
            "l2": "flushed between timed steps (256 MiB write)"}
+    # the step's second roofline: it moves ~5.2 GB of arenas through HBM per 1024 rays (ncu), next to its 900 GFLOP
+    hbm_peak, hbm_kind = measured_hbm()
+    step_bytes = NCU_TRAIN_STEP_DRAM_BYTES_1024 * n_rays / 1024.0
+    rec["hbm"] = {"dram_bytes_per_step": step_bytes, "achieved_gbs": step_bytes / (ms_step / 1e3) / 1e9, "peak_gbs": hbm_peak,
+                  "frac": step_bytes / (ms_step / 1e3) / 1e9 / hbm_peak, "peak_kind": hbm_kind + " copy bandwidth",
+                  "source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of the step's 8 MLP launches (profiles/train_r2z_metrics.txt), scaled by rays / 1024"}
     if not full:
         return rec
     ms_e2e = timed(step_e2e, steps, warm, "wall")

@@ -53,10 +53,12 @@ def up_to_date(out=OUT, sources=SOURCES):
     return os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == _digest(sources)
 
 
-def build_experiment(bits, verbose=False):
-    """Diagnostic flavour libnerf_b200_exp<bits>.so (-DNERF_EXP=bits: timing experiments that break results on purpose, see
-    csrc/tc_common.cuh); select it with NERF_B200_LIB=<path>.  Never the product library."""
-    return _build(OUT.replace(".so", "_exp%d.so" % bits), os.path.join(HERE, "build_exp%d" % bits), SOURCES, ["-DNERF_EXP=%d" % bits], verbose)
+def build_experiment(bits, verbose=False, defines=(), tag=None):
+    """Diagnostic flavour libnerf_b200_exp<bits>[_<tag>].so (-DNERF_EXP=bits plus `defines`: timing experiments, some of which
+    break results on purpose, see csrc/tc_common.cuh); select it with NERF_B200_LIB=<path>.  Never the product library."""
+    name = "exp%d%s" % (bits, "_" + tag if tag else "")
+    return _build(OUT.replace(".so", "_%s.so" % name), os.path.join(HERE, "build_" + name), SOURCES,
+                  ["-DNERF_EXP=%d" % bits] + ["-D" + d for d in defines], verbose)
 
 
 def build_trace(verbose=False):
@@ -113,6 +115,8 @@ if __name__ == "__main__":
         print(build_trace(verbose=True))
         sys.exit(0)
     if "--exp" in sys.argv:
-        print(build_experiment(int(sys.argv[sys.argv.index("--exp") + 1]), verbose=True))
+        defs = [sys.argv[i + 1] for i, a in enumerate(sys.argv) if a == "--define"]
+        tag = sys.argv[sys.argv.index("--tag") + 1] if "--tag" in sys.argv else None
+        print(build_experiment(int(sys.argv[sys.argv.index("--exp") + 1]), verbose=True, defines=defs, tag=tag))
         sys.exit(0)
     print(build(force="--force" in sys.argv, verbose=True, waitprof="--waitprof" in sys.argv))

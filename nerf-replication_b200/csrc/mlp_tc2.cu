@@ -191,7 +191,7 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
       uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      if (MODE != 2) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
+      if (MODE != 2 && !(NERF_EXP & 64)) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
     }
   }
 }
@@ -239,7 +239,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       uint8_t* gb = grow + (c0 >> 6) * 16384 + ((c0 & 63) >> 3) * 1024;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
+      if (!(NERF_EXP & 64)) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
     }
   };
   tmem_ld32(taddr, va);
@@ -394,7 +394,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
               {
                 const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
                 ++itb;
-                mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
+                if (!(NERF_EXP & 128)) mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
                 tc_fence_after();
                 if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | 2u, 1024, tn, 0, 3000);
                 issue_bias(tile, bslot);
@@ -510,6 +510,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
         }
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
+        if (SAVE) exp_bulk_wait(lane);
         const bool tr = SAVE && q == 0 && lane == 0;
         if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 1u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
         if (li < 9) {
@@ -523,6 +524,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
           if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 2u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
           signal_ready();
           if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 3u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
+          if (SAVE) exp_bulk_rows_to_arena(sAct, q, lane, tile_base + (size_t)(li < 8 ? arena::kActH + 4 * li : arena::kActFeat) * arena::kBlockBytes, 4);
           if (kDefer) {        // arena copy of this layer's output, its ReLU bit masks and (layer 5) PE(dir), off the critical path
             flush_row_to_arena(sAct, row_base, row_xor, grow, 4);
             if (li != 8) {

@@ -328,6 +328,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         }
         mbar_wait(&sb.acc_full[tile], lc & 1u, 0x40 + tile);
         tc_fence_after();
+        exp_bulk_wait(lane);
         if (s == S_PE5) {
           // d PE from the skip connection: park 64 fp32 columns in HBM until the end of the chain
           uint32_t v[32];
@@ -383,6 +384,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           else if (s == S_F) epi_masked<true>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
           else epi_masked<false>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
           if (i + 1 < kSteps) signal_ready(); else tc_fence_before();
+          exp_bulk_rows_to_arena(sA, q, lane, a.grad_arena + (size_t)T * arena::grad_tile_bytes() + (size_t)step_out_slot(s) * arena::kBlockBytes, 4);
           flush_row_to_arena(sA, row_base, row_xor, grow, 4);
         }
       }

@@ -352,6 +352,21 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 // ... have completed entirely (required before the CTA exits)
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// NERF_EXP bit 8 (timing experiment, build with bits 0 + 8 = 257; the arena then holds the swizzled operand image, which wgrad
+// does not understand): the warp's 32 rows of n_blocks A-operand blocks go to the arena as bulk async copies issued by one
+// lane after the hand-over, instead of 32 st.global.v4 per row in the epilogue -- what would a bulk-store arena buy?
+__device__ __forceinline__ void exp_bulk_rows_to_arena(const uint8_t* s_blk0, int q, int lane, uint8_t* g_blk0, int n_blocks) {
+  if (!(NERF_EXP & 256)) return;
+  if (lane == 0) {
+    for (int b = 0; b < n_blocks; ++b) bulk_s2g(g_blk0 + b * 16384 + q * 4096, s_blk0 + b * 16384 + q * 4096, 4096);
+    bulk_commit();
+  }
+}
+__device__ __forceinline__ void exp_bulk_wait(int lane) {
+  if (!(NERF_EXP & 256)) return;
+  if (lane == 0) bulk_wait_read0();
+  __syncwarp();
+}
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
