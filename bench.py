@@ -573,8 +573,15 @@ def train_record(args, eng, net0, cfg, rank, world, dev, n_rays, timed, barrier,
     teng.profile(True)
     teng.profile_read()
     k_steps = 10
+    step_device(0)
+    teng.profile_read()
+    pe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    pe[0].record()
     for i in range(k_steps):
         step_device(i)
+    pe[1].record()
+    torch.cuda.synchronize()
+    ms_step_plain = pe[0].elapsed_time(pe[1]) / k_steps        # plain launches with event brackets, no L2 flush in between
     cl = teng.profile_read_classes()
     teng.profile(False)
     n_c, n_f = n_rays * N_SAMPLES, n_rays * (N_SAMPLES + N_IMPORTANCE)
@@ -596,6 +603,10 @@ def train_record(args, eng, net0, cfg, rank, world, dev, n_rays, timed, barrier,
     rec["kernels"] = kernels
     rec["mlp_ms_per_step"] = sum(v["ms_per_step"] for v in kernels.values())
     rec["other_ms_per_step"] = ms_step - rec["mlp_ms_per_step"]
+    # everything that is not an MLP kernel (stage kernels, memset, clip/Adam/re-pack, launch gaps), measured in the SAME run as
+    # the class times: an upper bound of the stages' share (plain launches leave larger gaps than the graph replay)
+    rec["non_mlp_ms_per_step_plain_launches"] = ms_step_plain - rec["mlp_ms_per_step"]
+    rec["non_mlp_share_plain_launches"] = (ms_step_plain - rec["mlp_ms_per_step"]) / ms_step_plain
     rec["ncu_traffic_bytes_per_launch"] = NCU_TRAFFIC_BYTES["train"]
 
     # ---- data-parallel checks and the all-reduce's cost (N > 1) -------------------------------------------------------------

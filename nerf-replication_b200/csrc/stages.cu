@@ -13,6 +13,19 @@ namespace nerf {
 
 constexpr int kWarpsPerBlock = 4;
 constexpr float kEps = 1e-5f;
+// unroll factors of the per-ray loops over 32-sample blocks (S = 192 -> 6 blocks): the blocks' loads and double-precision exp
+// chains are independent, only the scan carry is serial -- but unrolling costs occupancy in the render kernels and buys
+// nothing in the 1024-ray training kernels (measured, see the defaults), so both stay at 1; the knobs remain for A/B builds.
+#ifndef NERF_STAGE_UNROLL_RENDER
+#define NERF_STAGE_UNROLL_RENDER 1      // measured on the 65 536-ray chunk: composite_kernel 88.6 us (1) / 137 us (3) / 120 us (6)
+#endif
+#ifndef NERF_STAGE_UNROLL_TRAIN
+#define NERF_STAGE_UNROLL_TRAIN 1       // 1024-ray step: composite_loss_bwd 16.0 us (1) / 17.3 us (6): no gain from unrolling either
+#endif
+constexpr int kUnrollRender = NERF_STAGE_UNROLL_RENDER, kUnrollTrain = NERF_STAGE_UNROLL_TRAIN;
+#ifndef NERF_PDF_MINBLOCKS
+#define NERF_PDF_MINBLOCKS 8            // sample_pdf_kernel, 65 536 rays: 184.6 us (8 CTAs/SM, 64 registers) / 201 us (6) / 197 us (10)
+#endif
 
 static inline int grid_for(int64_t n_rays, int num_sms) {
   int64_t blocks = (n_rays + kWarpsPerBlock - 1) / kWarpsPerBlock;
@@ -142,6 +155,7 @@ __global__ void composite_kernel(const float4* __restrict__ raw, const float* __
     const float4* rr = raw + ray * S;
     const float* tt = t + ray * S;
     float carry = 1.0f, sr = 0.f, sg = 0.f, sb = 0.f, sd = 0.f, sa = 0.f;
+#pragma unroll kUnrollRender      // independent loads / exp chains of consecutive 32-sample blocks overlap; same operations, same order
     for (int j = 0; j < nblk; ++j) {
       const int i = j * 32 + lane;
       const bool valid = i < S;
@@ -211,6 +225,7 @@ __device__ __forceinline__ float build_cdf(const float4* __restrict__ raw_c, con
   const int nblk = (Nc + 31) / 32;
   float carry = 1.0f, ssum = 0.f, sig_sum = 0.f, sig_max = 0.f;
   bool ert_seen = false;
+#pragma unroll 2
   for (int j = 0; j < nblk; ++j) {
     const int i = j * 32 + lane;
     const bool valid = i < Nc;
@@ -268,14 +283,9 @@ __device__ __forceinline__ float build_cdf(const float4* __restrict__ raw_c, con
 }
 
 struct FineSample { float t, u, c0, c1, b0, b1; int inds, below, above; };
-__device__ __forceinline__ FineSample inverse_cdf(const float* tc, const float* cdf, int Nc, float u) {
+// lo = searchsorted(cdf, u, right=True): first index with cdf > u
+__device__ __forceinline__ FineSample inverse_cdf_finish(const float* tc, const float* cdf, int Nc, float u, int lo) {
   FineSample f;
-  const int L = Nc - 1;
-  int lo = 0, hi = L;                         // searchsorted(right=True): first index with cdf > u
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
-  }
   f.inds = lo; f.u = u;
   f.below = min(max(lo - 1, 0), Nc - 3);      // the reference clamps at Nc-3 (volume_renderer.py:153-154)
   f.above = min(max(lo, 0), Nc - 3);
@@ -287,6 +297,31 @@ __device__ __forceinline__ FineSample inverse_cdf(const float* tc, const float* 
   const float tt = __fdiv_rn(__fsub_rn(u, f.c0), denom);
   f.t = __fadd_rn(f.b0, __fmul_rn(tt, __fsub_rn(f.b1, f.b0)));
   return f;
+}
+__device__ __forceinline__ FineSample inverse_cdf(const float* tc, const float* cdf, int Nc, float u) {
+  const int L = Nc - 1;
+  int lo = 0, hi = L;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  }
+  return inverse_cdf_finish(tc, cdf, Nc, u, lo);
+}
+
+// Nc == 64: cdf has 63 = 2^6 - 1 entries, so the search of inverse_cdf takes exactly six probes whatever u is; four samples
+// of a lane run their (identical) probe sequences interleaved instead of as four dependent shared-memory chains.
+__device__ __forceinline__ void search4_cdf63(const float* cdf, const float (&uu)[4], int (&lo)[4]) {
+  int hi[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { lo[j] = 0; hi[j] = 63; }
+#pragma unroll
+  for (int it = 0; it < 6; ++it) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int mid = (lo[j] + hi[j]) >> 1;
+      if (cdf[mid] <= uu[j]) lo[j] = mid + 1; else hi[j] = mid;
+    }
+  }
 }
 
 __device__ __forceinline__ float fine_u(const float* __restrict__ u_row, int philox, uint64_t seed, uint64_t call_id,
@@ -328,6 +363,39 @@ __device__ __forceinline__ bool warp_merge_sorted(const float* tc, float* keys, 
   for (int i = lane; i + 1 < Nc; i += 32) ok = ok && tc[i] <= tc[i + 1];
   for (int k = lane; k + 1 < Nf; k += 32) ok = ok && tf[k] <= tf[k + 1];
   if (!__all_sync(0xffffffffu, ok)) return false;
+  if (Nc == 64 && Nf == 128) {
+    // the default sampling: 2 coarse + 4 fine elements per lane.  The same probe sequences as the loops below, but with a fixed
+    // trip count (8 probes cover 128 entries, a converged search idles), so that the six searches of a lane interleave
+    // instead of running one dependent shared-memory chain after the other.
+    float v[6];
+    int lo[6], hi[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      v[j] = j < 2 ? tc[lane + 32 * j] : tf[lane + 32 * (j - 2)];
+      lo[j] = 0; hi[j] = j < 2 ? 128 : 64;
+    }
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        if (lo[j] < hi[j]) {
+          const int mid = (lo[j] + hi[j]) >> 1;
+          const bool right = j < 2 ? (tf[mid] < v[j]) : (tc[mid] <= v[j]);   // coarse: fine depths strictly below; fine: coarse at or below
+          if (right) lo[j] = mid + 1; else hi[j] = mid;
+        }
+      }
+    }
+    __syncwarp();                             // every probe of keys[Nc..] is done before the slots are overwritten
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const int src = j < 2 ? lane + 32 * j : Nc + lane + 32 * (j - 2);
+      const int dst = (j < 2 ? lane + 32 * j : lane + 32 * (j - 2)) + lo[j];
+      keys[dst] = v[j];
+      kidx[dst] = src;
+    }
+    __syncwarp();
+    return true;
+  }
   float val[kMergeSlots];
   int pos[kMergeSlots];
 #pragma unroll
@@ -363,7 +431,7 @@ __device__ __forceinline__ bool warp_merge_sorted(const float* tc, float* keys, 
   return true;
 }
 
-__global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float* __restrict__ t_c, int64_t n, int Nc,
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, NERF_PDF_MINBLOCKS) sample_pdf_kernel(const float4* __restrict__ raw_c, const float* __restrict__ t_c, int64_t n, int Nc,
                                   int Nf, int Npad, const float* __restrict__ u, int philox, uint64_t seed,
                                   uint64_t call_id, const float* __restrict__ cdf_in, float* __restrict__ t_fine,
                                   int64_t* __restrict__ inds, int64_t* __restrict__ below,
@@ -381,8 +449,7 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
     if (cdf_out) for (int k = lane; k < Nc - 1; k += 32) cdf_out[ray * (Nc - 1) + k] = s.cdf[k];
     __syncwarp();
     for (int k = lane; k < Nc; k += 32) { s.keys[k] = s.tc[k]; s.kidx[k] = k; }
-    for (int k = lane; k < Nf; k += 32) {
-      FineSample f = inverse_cdf(s.tc, s.cdf, Nc, fine_u(u ? u + ray * Nf : nullptr, philox, seed, call_id, ray, Nf, k));
+    auto emit = [&](int k, const FineSample& f) {
       s.keys[Nc + k] = f.t; s.kidx[Nc + k] = Nc + k;
       const int64_t o = ray * Nf + k;
       if (t_fine) t_fine[o] = f.t;
@@ -396,6 +463,26 @@ __global__ void sample_pdf_kernel(const float4* __restrict__ raw_c, const float*
         s.fvalid[k] = valid ? 1 : 0;
         if (prune.valid_fine) prune.valid_fine[o] = valid ? 1 : 0;
       }
+    };
+    const float* u_row = u ? u + ray * Nf : nullptr;
+    if (Nc == 64) {
+      for (int k0 = lane; k0 < Nf; k0 += 128) {
+        float uu[4];
+        int lo[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = k0 + 32 * j;
+          uu[j] = k < Nf ? fine_u(u_row, philox, seed, call_id, ray, Nf, k) : 0.f;
+        }
+        search4_cdf63(s.cdf, uu, lo);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = k0 + 32 * j;
+          if (k < Nf) emit(k, inverse_cdf_finish(s.tc, s.cdf, Nc, uu[j], lo[j]));
+        }
+      }
+    } else {
+      for (int k = lane; k < Nf; k += 32) emit(k, inverse_cdf(s.tc, s.cdf, Nc, fine_u(u_row, philox, seed, call_id, ray, Nf, k)));
     }
     for (int k = Nt + lane; k < Npad; k += 32) { s.keys[k] = __int_as_float(0x7f800000); s.kidx[k] = 0x7fffffff; }
     __syncwarp();
@@ -493,6 +580,7 @@ __device__ __forceinline__ RayMaps composite_fwd_pass(const float4* __restrict__
                                                       float* sT, float* sA, bool maps) {
   const int nblk = (S + 31) / 32;
   float carry = 1.0f, sr = 0.f, sg = 0.f, sb = 0.f, sd = 0.f, sa = 0.f;
+#pragma unroll kUnrollTrain
   for (int j = 0; j < nblk; ++j) {
     const int i = j * 32 + lane;
     const bool valid = i < S;
@@ -533,6 +621,7 @@ __device__ __forceinline__ void composite_bwd_ray(const float4* __restrict__ rr,
   const bool need_rgb = (g0 != 0.f) || (g1 != 0.f) || (g2 != 0.f);
   // suffix sums S_k = sum_{j>k} dw_j w_j
   float suffix_carry = 0.f;
+#pragma unroll kUnrollTrain
   for (int j = nblk - 1; j >= 0; --j) {
     const int i = j * 32 + lane;
     const bool valid = i < S;
@@ -708,8 +797,7 @@ __global__ void sample_pdf_bwd_kernel(const float4* __restrict__ raw_c, const fl
       if (idx >= Nc) dtf[idx - Nc] = __ldg(d_t_sorted + ray * Nt + p);
     }
     __syncwarp();
-    for (int k = lane; k < Nf; k += 32) {
-      FineSample f = inverse_cdf(s.tc, s.cdf, Nc, fine_u(u ? u + ray * Nf : nullptr, philox, seed, call_id, ray, Nf, k));
+    auto scatter = [&](int k, const FineSample& f) {
       const float g = dtf[k];
       const float db = __fsub_rn(f.b1, f.b0);
       const float den_raw = __fsub_rn(f.c1, f.c0);
@@ -723,6 +811,26 @@ __global__ void sample_pdf_bwd_kernel(const float4* __restrict__ raw_c, const fl
       }
       atomicAdd(&dcdf[f.below], d_c0);
       atomicAdd(&dcdf[f.above], d_c1);
+    };
+    const float* u_row = u ? u + ray * Nf : nullptr;
+    if (Nc == 64) {
+      for (int k0 = lane; k0 < Nf; k0 += 128) {
+        float uu[4];
+        int lo[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = k0 + 32 * j;
+          uu[j] = k < Nf ? fine_u(u_row, philox, seed, call_id, ray, Nf, k) : 0.f;
+        }
+        search4_cdf63(s.cdf, uu, lo);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = k0 + 32 * j;
+          if (k < Nf) scatter(k, inverse_cdf_finish(s.tc, s.cdf, Nc, uu[j], lo[j]));
+        }
+      }
+    } else {
+      for (int k = lane; k < Nf; k += 32) scatter(k, inverse_cdf(s.tc, s.cdf, Nc, fine_u(u_row, philox, seed, call_id, ray, Nf, k)));
     }
     __syncwarp();
     // dpdf_j = sum_{k>j} dcdf_k, j in [0, Nc-2);  dot = sum_j dpdf_j pdf_j

@@ -21,17 +21,21 @@ def _per_tensor(oracle, flat):
     return out
 
 
-@pytest.mark.parametrize("weights", ["fog", "sharp", "seed0"])
+@pytest.mark.parametrize("weights", ["fog", "fog_seed3", "fog_dense", "sharp", "seed0"])
 def test_gradients_match_reference_autograd(oracle, weights):
     """Engine gradients vs torch autograd on the oracle (the reference graph incl. the un-detached t_fine path).
     fine net: 1e-3 of each tensor's max (or the fp32 noise floor where that is larger).
     coarse net: its only signal is d loss / d t_fine through the inverse CDF.  With near-empty bins (seed0 /
     sharp weights) that gradient is noise-dominated in fp32 -- the oracle itself moves by 20%..500% between fp32
     and fp64 (measured: oracle.grads_fp64) -- so there the bound is the oracle's own fp32-vs-fp64 distance;
-    the "fog" weights (sigma ~ 1 everywhere, smooth CDF) are well conditioned and held to 2e-2 of max."""
-    sd = {"fog": oracle.fog_state_dict(0), "sharp": oracle.init_state_dict(0, sharp=True), "seed0": oracle.init_state_dict(0)}[weights]
+    the "fog" weights (sigma ~ 1 everywhere, smooth CDF) are well conditioned and held to 2e-2 of max.  Two more such sets
+    (another seed and ray batch; a denser fog) verify the un-detached t_fine path on more than one: there the oracle's own
+    fp32-vs-fp64 distance is 0.8 % / 1.2 % of max (fog: 0.65 %), so the bound is max(2e-2, 2 x that distance)."""
+    sd = {"fog": lambda: oracle.fog_state_dict(0), "fog_seed3": lambda: oracle.fog_state_dict(3),
+          "fog_dense": lambda: oracle.fog_state_dict(0, bias=1.5), "sharp": lambda: oracle.init_state_dict(0, sharp=True),
+          "seed0": lambda: oracle.init_state_dict(0)}[weights]()
     n = 32
-    o, d, gt, _, _ = oracle.synthetic_train_batch(0, 0, n, 100, 100)
+    o, d, gt, _, _ = oracle.synthetic_train_batch({"fog_seed3": 5}.get(weights, 0), 0, n, 100, 100)
     tr = oracle.Trainer(sd)
     loss_ref = tr.forward_backward(o, d, gt)
     g_ref = tr.grads_flat()
@@ -58,7 +62,12 @@ def test_gradients_match_reference_autograd(oracle, weights):
         # ill-conditioned sets: +-1..4 ulp weight perturbations move the fp32 oracle's own coarse gradients by
         # 0.5%..8% of max per tensor (event-driven: single searchsorted flips / tiny denominators), so the coarse
         # bound there is max(noise floor, 15% of max); the fixed bounds apply to fog (coarse) and to every fine tensor
-        tol = fixed if (coarse and weights == "fog") else max(fixed, 1.5 * noise, (0.15 * scale) if coarse else 0.0)
+        if coarse and weights == "fog":
+            tol = fixed
+        elif coarse and weights.startswith("fog"):
+            tol = max(fixed, 2.0 * noise)
+        else:
+            tol = max(fixed, 1.5 * noise, (0.15 * scale) if coarse else 0.0)
         err = maxabs(got_t[k], ref_t[k])
         if err > tol:
             bad.append((k, err, tol, scale, noise))
