@@ -46,7 +46,16 @@ constexpr int kRingReal = 3;
 constexpr int kRing = kRingReal + ((NERF_EXP >> 3) & 3);
 constexpr int kNumSched = 10;                   // L0..L7, FEAT, VIEWS
 constexpr int kNumStages = 39;
-constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 168 registers per thread
+// One warp can issue one bulk / TMA copy (expect_tx + cp.async.bulk.tensor) per ~300-450 clk whatever its size, several warps
+// issue in parallel (profiles/ubench/handshake.cu: 307 -> 154 -> 102 -> 77 clk per 1 KB stage with 1 / 2 / 3 / 4 issuing warps;
+// 16 KB stages then reach 86 B/clk/SM).  A single producer warp paced the per-tile (training) order at ~870 clk per stage
+// against 512 clk of MMAs, so the weight ring is fed by kNumProd warps, warp p taking the stages it % kNumProd == p.
+#ifndef NERF_NUM_PROD
+#define NERF_NUM_PROD 3
+#endif
+constexpr int kNumProd = NERF_NUM_PROD;
+constexpr int kFirstExtraProd = 10;   // warps: 0 producer 0, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps (TMEM lane quarter = warp % 4), 10.. producers 1..
+constexpr int kThreads = 320 + 32 * (kNumProd - 1);      // 384 threads -> still 168 registers per thread
 constexpr int kOnesBytes = 4096;                // constant A slab of the bias MMA: 128 rows x 16 k, columns 0..2 = 1.0
 constexpr int kBiasSlabBytes = 8192;            // packed bias slab of one schedule entry (both halves), mlp_tc.cu pack_bias_slabs_kernel
 constexpr uint32_t kOffA = 0, kOffPE = 131072, kOffW = 163840;
@@ -76,6 +85,7 @@ struct Bars {
 
 __device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk, uint32_t a,
                                             uint32_t b, uint32_t c, uint32_t d) {
+  if (NERF_EXP & 1024) return;     // timing experiment: the epilogues write no A operand
   *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
 }
 
@@ -313,30 +323,43 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
   tc_fence_after();
   const uint32_t tmem = sb.tmem_slot;
 
-  if (warp == 0) {
-    // ===== weight producer (both CTAs): my half of every stage =====
-    if (lane == 0) {
+  const int prod = warp == 0 ? 0 : (warp >= kFirstExtraProd ? warp - kFirstExtraProd + 1 : -1);
+  if (prod >= 0) {
+    // ===== weight producers (both CTAs): my half of every stage; producer p issues the stages it % kNumProd == p, the last
+    // one also the bias slabs =====
+    // The whole warp runs the loop converged (all lanes poll the barrier, lane 0 issues): a lone lane-0 loop inside a diverged
+    // warp sees its barrier complete ~2 000 clk late (event trace, profiles/exp_train_r2.md).
+    {
       uint32_t it = 0, itb = 0, tn_p = 0;
       const uint32_t w_full_leader = mapa_u32(smem_u32(&sb.w_full[0]), 0);
       for (int64_t st = pair0; st < n_pair; st += pair_stride) {
         for (int li = 0; li < kNumSched; ++li) {
-          const uint32_t bytes = (uint32_t)sched_n(li) * 64u;                 // half of the stage: N/2 rows x 128 B
+          // half of the stage: N/2 rows x 128 B (NERF_EXP bit 11, timing experiment: 8 rows = 1 KB only, same handshakes)
+          const uint32_t bytes = (NERF_EXP & 2048) ? 1024u : (uint32_t)sched_n(li) * 64u;
           for (int rep = 0; rep < kReps; ++rep) {                             // training: once per tile (see the issuer)
-            {                                                                 // the layer's bias slab (N/2 rows x 32 B), own ring
+            if (prod == kNumProd - 1) {                                       // the layer's bias slab (N/2 rows x 32 B), own ring
               const uint32_t slot = itb % kBiasRing, par = (itb / kBiasRing) & 1u;
-              ++itb;
               mbar_wait(&sb.b_empty[slot], par ^ 1u, 0x18 + slot);
-              mbar_arrive_expect_tx(&sb.b_full[slot], bytes / 4);
-              bulk_g2s(smem + kOffBiasRing + slot * 4096, wbias + (size_t)li * kBiasSlabBytes + (size_t)rank * 4096, bytes / 4, &sb.b_full[slot]);
+              if (lane == 0) {
+                mbar_arrive_expect_tx(&sb.b_full[slot], bytes / 4);
+                bulk_g2s(smem + kOffBiasRing + slot * 4096, wbias + (size_t)li * kBiasSlabBytes + (size_t)rank * 4096, bytes / 4, &sb.b_full[slot]);
+              }
+              __syncwarp();
             }
+            ++itb;
             for (int kb = 0; kb < sched_nkb(li); ++kb, ++it) {
+              if ((int)(it % kNumProd) != prod) continue;
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
               mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
-              trace_event(0x3000u | (rep << 8) | (li << 4) | (4u + kb), 1024, tn_p, 3000, 5000);
-              // both halves complete on the leader's barrier, which expects the bytes of the pair
-              if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
-              tma_stage_cg2(smem + ring_slot_off(slot), sched_n(li) == 256 ? &tm128 : &tm64,
-                            stage_row0 + (sched_start(li) + kb) * 256 + (int)rank * (sched_n(li) / 2), w_full_leader + slot * 8u);
+              if (lane == 0) {
+                if (prod == 0) trace_event(0x3000u | (rep << 8) | (li << 4) | (4u + kb), 1024, tn_p, 3000, 5000);
+                // both halves complete on the leader's barrier, which expects the bytes of the pair
+                if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
+                tma_stage_cg2(smem + ring_slot_off(slot), sched_n(li) == 256 ? &tm128 : &tm64,
+                              stage_row0 + (sched_start(li) + kb) * 256 + (int)rank * (sched_n(li) / 2), w_full_leader + slot * 8u);
+                if (prod == 0) trace_event(0x3000u | (rep << 8) | (li << 4) | (9u + kb), 1024, tn_p, 3000, 5000);      // load issued
+              }
+              __syncwarp();
             }
           }
         }
@@ -344,8 +367,8 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
     }
     __syncwarp();
   } else if (warp == 1 && rank == 1) {
-    // ===== forwarder (peer CTA): relay the arrival of my half of a bias slab to the leader's b_full =====
-    if (lane == 0) {
+    // ===== forwarder (peer CTA): relay the arrival of my half of a bias slab to the leader's b_full (converged warp) =====
+    {
       uint32_t itb = 0;
       for (int64_t st = pair0; st < n_pair; st += pair_stride)
         for (int li = 0; li < kNumSched; ++li)
@@ -353,7 +376,8 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
             const uint32_t bslot = itb % kBiasRing, bpar = (itb / kBiasRing) & 1u;
             ++itb;
             mbar_wait(&sb.b_full[bslot], bpar, 0x58 + bslot);
-            mbar_arrive_remote(mapa_u32(smem_u32(&sb.b_full[bslot]), 0));
+            if (lane == 0) mbar_arrive_remote(mapa_u32(smem_u32(&sb.b_full[bslot]), 0));
+            __syncwarp();
           }
     }
     __syncwarp();
@@ -377,11 +401,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
             const int ablk = a_block(kb);
             const uint32_t a_base = ablk < 0 ? sPE + tile * 16384u : sA + tile * 65536u + (uint32_t)ablk * 16384u;
             const uint32_t b_base = smem_u32(smem) + ring_slot_off(slot);
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-              umma_ss2_w(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
-                       make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, 1u);
-            }
+            umma_ss2_w_x4(tmem + tile * 256u, make_smem_desc(a_base, 16, 1024, kLayoutSW128), make_smem_desc(b_base, 16, 1024, kLayoutSW128), idesc, 1u);
           };
           if (kPerTile) {
             // Training forward: one tile's whole layer, then the other's -- the layer's weights are streamed twice (L2
@@ -590,7 +610,7 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
     const cuuint64_t gdim[2] = {64u << kTmaRowShift, ((cuuint64_t)n_rep * 2 * kNumStages * 256) >> kTmaRowShift}, gstride[1] = {128u << kTmaRowShift};
     const cuuint32_t estr[2] = {1, 1};
     for (int v = 0; v < 2; ++v) {
-      const cuuint32_t box[2] = {64u << kTmaRowShift, (v == 0 ? 128u : 64u) >> kTmaRowShift};
+      const cuuint32_t box[2] = {64u << kTmaRowShift, (NERF_EXP & 2048) ? 8u : ((v == 0 ? 128u : 64u) >> kTmaRowShift)};
       CUresult r = reinterpret_cast<EncodeFn>(fn)(v == 0 ? &tm128 : &tm64, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(stage_base), gdim, gstride, box, estr,
                                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

@@ -43,6 +43,7 @@ namespace bw {
 
 __device__ __forceinline__ void store_chunk(uint8_t* blk, uint32_t row_base, uint32_t row_xor, int chunk, uint32_t a,
                                             uint32_t b, uint32_t c, uint32_t d) {
+  if (NERF_EXP & 1024) return;     // timing experiment: the epilogues write no A operand
   *reinterpret_cast<uint4*>(blk + row_base + (((uint32_t)chunk ^ row_xor) << 4)) = make_uint4(a, b, c, d);
 }
 constexpr float kInv2PiHi = 0.15915493667125702f, kInv2PiLo = 6.4206382432985265e-09f;
@@ -189,7 +190,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 
   if (warp == 0) {
     // ===== weight producer =====
-    if (lane == 0) {
+    // The whole warp runs the loop converged (all lanes poll the barrier, lane 0 issues): a lone lane-0 loop inside a diverged
+    // warp sees its barrier complete ~2 000 clk late (event trace of the forward, profiles/exp_train_r2.md).
+    {
       uint32_t it = 0;
       for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
         for (int i = 0; i < kSteps; ++i) {
@@ -199,24 +202,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           for (int kb = 0; kb < step_nkb(s); ++kb, ++it) {
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
             mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
-            mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
-            bulk_g2s(smem + kOffW + slot * kHalfBytes,
-                     reinterpret_cast<const uint8_t*>(a.wpack) + (size_t)(step_stage0(s) + kb) * kStageImage + (size_t)rank * bytes,
-                     bytes, &sb.w_full[slot]);
+            if (lane == 0) {
+              mbar_arrive_expect_tx(&sb.w_full[slot], bytes);
+              bulk_g2s(smem + kOffW + slot * kHalfBytes,
+                       reinterpret_cast<const uint8_t*>(a.wpack) + (size_t)(step_stage0(s) + kb) * kStageImage + (size_t)rank * bytes,
+                       bytes, &sb.w_full[slot]);
+            }
+            __syncwarp();
           }
         }
     }
     __syncwarp();
   } else if (warp == 1 && rank == 1) {
-    // ===== forwarder =====
-    if (lane == 0) {
+    // ===== forwarder (converged warp, see the producer) =====
+    {
       uint32_t it = 0;
       for (int64_t st = pair0; st < a.n_pair; st += pair_stride)
         for (int i = 0; i < kSteps; ++i)
           for (int kb = 0; kb < 2 * step_nkb(step_at(i)); ++kb, ++it) {
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
             mbar_wait(&sb.w_full[slot], par, 0x50 + slot);
-            mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+            if (lane == 0) mbar_arrive_remote(mapa_u32(smem_u32(&sb.w_full[slot]), 0));
+            __syncwarp();
           }
     }
     __syncwarp();
@@ -241,10 +248,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
               tc_fence_after();
               const uint32_t a_base = sA + tile * 65536u + (uint32_t)kb * 16384u;
               const uint32_t b_base = sW + slot * kHalfBytes;
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                umma_ss2_w(tmem + tile * 256u, make_smem_desc(a_base + kk * 32, 16, 1024, kLayoutSW128),
-                         make_smem_desc(b_base + kk * 32, 16, 1024, kLayoutSW128), idesc, (kb | kk) != 0);
+              umma_ss2_w_x4(tmem + tile * 256u, make_smem_desc(a_base, 16, 1024, kLayoutSW128), make_smem_desc(b_base, 16, 1024, kLayoutSW128), idesc, kb != 0);
               umma_commit2_w(&sb.w_empty[slot], 0x3);
             }
             umma_commit2_w(&sb.acc_full[tile], 0x3);

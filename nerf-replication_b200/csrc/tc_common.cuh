@@ -60,8 +60,30 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// NERF_MBAR_POLL (A/B builds): 0 = mbarrier.try_wait (may suspend the thread for a system-dependent time), 1 = mbarrier.test_wait
+// (never suspends: pure polling), N > 1 = try_wait with suspendTimeHint = N ns
+#ifndef NERF_MBAR_POLL
+#define NERF_MBAR_POLL 0
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
+#if NERF_MBAR_POLL == 1
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+#elif NERF_MBAR_POLL > 1
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"((uint32_t)NERF_MBAR_POLL)
+      : "memory");
+#else
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -69,6 +91,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
+#endif
   return ok != 0;
 }
 static __device__ __noinline__ void mbar_timeout(uint32_t tag, uint32_t parity) {
@@ -292,7 +315,11 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
+#if NERF_MBAR_POLL == 1
+      "mbarrier.test_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+#else
       "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+#endif
       "selp.b32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)
@@ -374,12 +401,34 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
 // loop inside `if (lane == 0)` every operand lives in a per-thread register and each tcgen05 instruction costs an
 // ELECT + R2UR.BROADCAST + BRA.U.ANY sequence (~22 SASS instructions, ~100 clk of the issuing thread per 128-clk MMA).
 __device__ __forceinline__ void umma_ss2_w(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  if (NERF_EXP & 512) return;      // timing experiment: no MMAs at all (the commits then complete at once)
   asm volatile(
       "{\n\t.reg .pred p, pe;\n\t"
       "elect.sync _|pe, 0xffffffff;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
       "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// The four K = 16 MMAs of one 64-wide k-block in ONE election: the operand descriptors advance by 32 bytes (2 address units)
+// per MMA.  Issued one by one through umma_ss2_w, every MMA costs an ELECT, a VOTEU and six R2UR.BROADCAST (the descriptors
+// are recomputed in vector registers: ~20 SASS instructions, ~600-850 clk of the issuing warp per 512-clk stage, which paced
+// the per-tile order of the training kernels).
+__device__ __forceinline__ void umma_ss2_w_x4(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate_first) {
+  if (NERF_EXP & 512) return;
+  asm volatile(
+      "{\n\t.reg .pred p, pe;\n\t.reg .b64 da, db;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "setp.eq.b32 p, 0, 0;\n\t"
+      "add.u64 da, %1, 2;\n\tadd.u64 db, %2, 2;\n\t"
+      "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n\t"
+      "add.u64 da, %1, 4;\n\tadd.u64 db, %2, 4;\n\t"
+      "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n\t"
+      "add.u64 da, %1, 6;\n\tadd.u64 db, %2, 6;\n\t"
+      "@pe tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate_first)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit2_w(uint64_t* bar, uint16_t mask) {

@@ -37,7 +37,8 @@ def main():
     names = {1: {1: "act_ready seen", 2: "bias slab seen", 3: "tile-layer issued + commit", 4: "stage 0 seen", 5: "stage 1 seen", 6: "stage 2 seen",
                  7: "stage 3 seen", 8: "stage 4 seen"},
              2: {1: "accumulator seen", 2: "epilogue done", 3: "hand-over signalled"},
-             3: {4: "slot free for stage 0", 5: "slot free for stage 1", 6: "slot free for stage 2", 7: "slot free for stage 3", 8: "slot free for stage 4"}}
+             3: {4: "slot free for stage 0", 5: "slot free for stage 1", 6: "slot free for stage 2", 7: "slot free for stage 3", 8: "slot free for stage 4",
+                 9: "load of stage 0 issued", 10: "load of stage 1 issued", 11: "load of stage 2 issued", 12: "load of stage 3 issued", 13: "load of stage 4 issued"}}
     last = {}
     lo, hi = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (0, 400)
     for t, tag in ev[lo:hi]:
