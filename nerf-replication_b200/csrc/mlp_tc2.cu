@@ -336,6 +336,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
         for (int li = 0; li < kNumSched; ++li) {
           // half of the stage: N/2 rows x 128 B (NERF_EXP bit 11, timing experiment: 8 rows = 1 KB only, same handshakes)
           const uint32_t bytes = (NERF_EXP & 2048) ? 1024u : (uint32_t)sched_n(li) * 64u;
+          const int row_li = stage_row0 + sched_start(li) * 256 + (int)rank * (sched_n(li) / 2);
           for (int rep = 0; rep < kReps; ++rep) {                             // training: once per tile (see the issuer)
             if (prod == kNumProd - 1) {                                       // the layer's bias slab (N/2 rows x 32 B), own ring
               const uint32_t slot = itb % kBiasRing, par = (itb / kBiasRing) & 1u;
@@ -356,7 +357,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
                 // both halves complete on the leader's barrier, which expects the bytes of the pair
                 if (rank == 0) mbar_arrive_expect_tx(&sb.w_full[slot], 2 * bytes);
                 tma_stage_cg2(smem + ring_slot_off(slot), sched_n(li) == 256 ? &tm128 : &tm64,
-                              stage_row0 + (sched_start(li) + kb) * 256 + (int)rank * (sched_n(li) / 2), w_full_leader + slot * 8u);
+                              row_li + kb * 256, w_full_leader + slot * 8u);
                 if (prod == 0) trace_event(0x3000u | (rep << 8) | (li << 4) | (9u + kb), 1024, tn_p, 3000, 5000);      // load issued
               }
               __syncwarp();

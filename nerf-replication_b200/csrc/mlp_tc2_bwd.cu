@@ -188,8 +188,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   tc_fence_after();
   const uint32_t tmem = sb.tmem_slot;
 
-  if (warp == 0) {
-    // ===== weight producer =====
+  const int prod = warp == 0 ? 0 : (warp >= kFirstExtraProd ? warp - kFirstExtraProd + 1 : -1);
+  if (prod >= 0) {
+    // ===== weight producers: producer p issues the stages it % kNumProd == p =====
     // The whole warp runs the loop converged (all lanes poll the barrier, lane 0 issues): a lone lane-0 loop inside a diverged
     // warp sees its barrier complete ~2 000 clk late (event trace of the forward, profiles/exp_train_r2.md).
     {
@@ -200,6 +201,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           const uint32_t bytes = (uint32_t)step_n(s) * 64u;
           for (int rep = 0; rep < 2; ++rep)            // once per tile: see the issuer
           for (int kb = 0; kb < step_nkb(s); ++kb, ++it) {
+            if ((int)(it % kNumProd) != prod) continue;
             const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
             mbar_wait(&sb.w_empty[slot], par ^ 1u, 0x10 + slot);
             if (lane == 0) {

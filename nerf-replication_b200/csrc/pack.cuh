@@ -105,7 +105,13 @@ constexpr int kRowsPerPair = 512;
 constexpr int kStageImage = 32768;
 constexpr int kHalfBytes = 16384;
 constexpr int kRing = 6;        // weight stages in flight
-constexpr int kThreads = 320;      // 10 warps: 0 producer, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps -> 200 registers per thread
+// weight producers: warp 0 and warps 10.. (one warp issues one bulk copy per ~300-450 clk whatever its size: see mlp_tc2.cu)
+#ifndef NERF_NUM_PROD_BWD
+#define NERF_NUM_PROD_BWD 3
+#endif
+constexpr int kNumProd = NERF_NUM_PROD_BWD;
+constexpr int kFirstExtraProd = 10;
+constexpr int kThreads = 320 + 32 * (kNumProd - 1);      // warps: 0 producer 0, 1 issuer / forwarder (+ TMEM alloc), 2-9 tile warps, 10.. producers 1..
 constexpr int kNumSteps = 11;      // V1, F, L7, L6, PE5, L5, L4, L3, L2, L1, P0
 constexpr int kNumStages = 42;
 enum Step { S_V1 = 0, S_F = 1, S_L7 = 2, S_L6 = 3, S_PE5 = 4, S_L5 = 5, S_L4 = 6, S_L3 = 7, S_L2 = 8, S_L1 = 9, S_P0 = 10 };
