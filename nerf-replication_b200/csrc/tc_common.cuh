@@ -265,7 +265,14 @@ __device__ __forceinline__ uint32_t mask2_from_bits(uint32_t bits, int i) {
 #endif
 __device__ __forceinline__ void st_global_cs(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   if (NERF_EXP & 1) return;
-  asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+#ifndef NERF_ARENA_ST
+#define NERF_ARENA_ST "st.global.cs.v4.b32"      // A/B builds: .cg / .wt / default write-back measured no faster
+#endif
+  if (NERF_EXP & 4096) {      // timing experiment: the same number of store instructions, a quarter of the bytes
+    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(a ^ b ^ c ^ d) : "memory");
+    return;
+  }
+  asm volatile(NERF_ARENA_ST " [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
