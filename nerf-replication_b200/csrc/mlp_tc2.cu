@@ -195,13 +195,11 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&v)[32], int c0,
 #pragma unroll
   for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
   if (grow) {
-    if (NERF_DEFER_STORES) {          // arena copy + mask words after the hand-over (flush_row_to_arena)
-      if (MODE != 2) mbits[c0 >> 5] = pos_bits32(pk);
-    } else {
+    if (MODE != 2 && !(NERF_EXP & 64)) mbits[c0 >> 5] = pos_bits32(pk);      // the row's mask record is stored once per layer
+    if (!NERF_DEFER_STORES) {         // (deferred flavour: arena copy after the hand-over, flush_row_to_arena)
       uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      if (MODE != 2 && !(NERF_EXP & 64)) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
     }
   }
 }
@@ -223,6 +221,7 @@ __device__ __forceinline__ void epi_layer(uint32_t taddr, const float* __restric
     if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
     epi_chunk<MODE>(vb, (c + 1) * 32, s_walpha, sigma, sAct, row_base, row_xor, grow, gmask, mbits);
   }
+  if (gmask && MODE != 2 && !NERF_DEFER_STORES) st_global_mask8(gmask, mbits);
 }
 
 // View-branch epilogue: 128 columns, ReLU, then the 128 -> 3 rgb head on CUDA cores.
@@ -230,6 +229,7 @@ template <bool SAVE>
 __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restrict__ s_wrgb,
                                           float& r0, float& r1, float& r2, uint8_t* grow, uint8_t* gmask) {
   uint32_t va[32], vb[32];
+  uint32_t mv[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};      // 128 columns: words 0..3 of the row's mask record
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
@@ -249,7 +249,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
       uint8_t* gb = grow + (c0 >> 6) * 16384 + ((c0 & 63) >> 3) * 1024;
 #pragma unroll
       for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-      if (!(NERF_EXP & 64)) *reinterpret_cast<uint32_t*>(gmask + (c0 >> 5) * arena::kMaskWordStride) = pos_bits32(pk);
+      if (!(NERF_EXP & 64)) mv[c0 >> 5] = pos_bits32(pk);
     }
   };
   tmem_ld32(taddr, va);
@@ -262,6 +262,7 @@ __device__ __forceinline__ void epi_views(uint32_t taddr, const float* __restric
     if (c + 2 < 4) tmem_ld32(taddr + (c + 2) * 32, va);
     chunk(vb, (c + 1) * 32);
   }
+  if (SAVE) st_global_mask8(gmask, mv);
 }
 
 // TMA tile load of this CTA's half of a weight stage (rows [row0, row0 + box rows) of the packed image seen as a
@@ -509,7 +510,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
       // training forward: this row's slice of the tile's arena blocks / bit-mask records (tc_arena.cuh)
       uint8_t* tile_base = SAVE ? act_arena + (size_t)((st * 2 + rank) * 2 + tile) * arena::act_tile_bytes() : nullptr;
       uint8_t* grow0 = SAVE ? tile_base + arena::cm_row_offset(row) : nullptr;
-      uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * 4 : nullptr;
+      uint8_t* gmask0 = SAVE ? tile_base + arena::act_mask_offset() + row * arena::kMaskRowBytes : nullptr;
       auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
       auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
       constexpr bool kDefer = SAVE && NERF_DEFER_STORES;
@@ -548,11 +549,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
           if (SAVE) exp_bulk_rows_to_arena(sAct, q, lane, tile_base + (size_t)(li < 8 ? arena::kActH + 4 * li : arena::kActFeat) * arena::kBlockBytes, 4);
           if (kDefer) {        // arena copy of this layer's output, its ReLU bit masks and (layer 5) PE(dir), off the critical path
             flush_row_to_arena(sAct, row_base, row_xor, grow, 4);
-            if (li != 8) {
-              uint8_t* gm = gmsk(arena::kMaskH + li);
-#pragma unroll
-              for (int w = 0; w < 8; ++w) *reinterpret_cast<uint32_t*>(gm + w * arena::kMaskWordStride) = mbits[w];
-            }
+            if (li != 8) st_global_mask8(gmsk(arena::kMaskH + li), mbits);
             if (li == 5) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPEDir));
           }
         } else {

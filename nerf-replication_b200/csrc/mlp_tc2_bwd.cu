@@ -278,9 +278,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
     // load issued just before the accumulator wait would expose its full HBM latency every step.
     auto load_mask_at = [&](int64_t st_, int layer, uint32_t (&mw)[8]) {
       const int64_t T_ = (st_ * 2 + rank) * 2 + tile;
-      const uint8_t* mp = a.act_arena + (size_t)T_ * arena::act_tile_bytes() + arena::act_mask_offset() + row * 4 + layer * arena::kMaskLayerBytes;
+      const uint8_t* mp = a.act_arena + (size_t)T_ * arena::act_tile_bytes() + arena::act_mask_offset() + row * arena::kMaskRowBytes + layer * arena::kMaskLayerBytes;
+      if (NERF_EXP & 4) {
 #pragma unroll
-      for (int w = 0; w < 8; ++w) mw[w] = (NERF_EXP & 4) ? 0xFFFFFFFFu : __ldg(reinterpret_cast<const uint32_t*>(mp + w * arena::kMaskWordStride));
+        for (int w = 0; w < 8; ++w) mw[w] = 0xFFFFFFFFu;
+      } else {
+        ld_global_mask8(mp, mw);
+      }
     };
     uint32_t mw_pre[8];
     if (pair0 < a.n_pair) load_mask_at(pair0, kInitMask, mw_pre);

@@ -28,15 +28,16 @@ constexpr int kActFeat = 33;     // feature_linear output (linear), 4 blocks
 constexpr int kActPEDir = 37;    // PE(dir): 27 values, column 63 = 1.0
 constexpr int kActHV = 38;       // views hidden (post-ReLU), 2 blocks
 constexpr int kActBlocks = 40;
-// ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][word 0..7][row 0..127] uint32 (a warp's
-//      word store / load covers 128 contiguous bytes); word w of a row covers columns [32 w, 32 w + 32):
+// ---- ReLU bit masks, stored behind the tile's activation blocks: [mask layer][row 0..127][word 0..7] uint32 -- one 32-byte
+//      record per row and layer, written / read with ONE 256-bit st.global / ld.global per row (a warp covers 1 KB of full
+//      sectors; round 2 first kept [layer][word][row] with eight 4-byte accesses per row); word w covers columns [32 w, 32 w + 32):
 //      column pair i (columns 32 w + 2 i, + 1) has its two flags at bits 8 (i & 1) + 7 - (i >> 1) and that + 16
 //      (tc_common.cuh pos_bits32 / mask2_from_bits: the consumer expands a pair with one shift-shared PRMT)
 constexpr int kMaskH = 0;        // h_l > 0, l = 0..7
 constexpr int kMaskHV = 8;       // views hidden > 0 (words 0..3)
 constexpr int kMaskLayers = 9;
-constexpr int kMaskWordStride = 128 * 4;       // bytes between consecutive words of one row
-constexpr int kMaskLayerBytes = 8 * kMaskWordStride;
+constexpr int kMaskRowBytes = 32;              // eight words of one row, contiguous
+constexpr int kMaskLayerBytes = 128 * kMaskRowBytes;
 // ---- gradient arena (written by the dgrad chain) : block slots per tile
 constexpr int kGradZ = 0;        // dZ_l (grad wrt pre-activation of trunk layer l), l = 0..7 : slots 4 l + b
 constexpr int kGradFeat = 32;    // grad wrt feature_linear output, 4 blocks

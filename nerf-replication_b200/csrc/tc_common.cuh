@@ -275,6 +275,18 @@ __device__ __forceinline__ void st_global_cs(void* p, uint32_t a, uint32_t b, ui
   asm volatile(NERF_ARENA_ST " [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// one row's 32-byte bit-mask record (tc_arena.cuh): 256-bit global store / read-only load (sm_100: STG.256 / LDG.256)
+__device__ __forceinline__ void st_global_mask8(void* p, const uint32_t (&m)[8]) {
+  if (NERF_EXP & 64) return;
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(m[0]), "r"(m[1]), "r"(m[2]), "r"(m[3]), "r"(m[4]),
+               "r"(m[5]), "r"(m[6]), "r"(m[7])
+               : "memory");
+}
+__device__ __forceinline__ void ld_global_mask8(const void* p, uint32_t (&m)[8]) {
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(m[0]), "=r"(m[1]), "=r"(m[2]), "=r"(m[3]), "=r"(m[4]), "=r"(m[5]), "=r"(m[6]), "=r"(m[7])
+               : "l"(p));
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   uint32_t r;
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
