@@ -588,7 +588,14 @@ int mlp_tc2_forward(NerfEngine* h, int net, const RowSrc& src, float* raw, uint8
     attr_set = true;
   }
   const int64_t n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
-  const int grid = 2 * (int)std::min<int64_t>(n_pair, h->num_sms / 2);
+  // the fewest CTA pairs that keep the number of waves (1 024 training rays: 384 pair tiles = 6 waves on 74 pairs as on 64):
+  // every pair then runs the same number of tiles and the idle SMs give their power budget to the busy ones
+  const int64_t max_pairs = h->num_sms / 2, waves = (n_pair + max_pairs - 1) / max_pairs;
+#ifdef NERF_FULL_GRID      // A/B builds: every pair the device has
+  const int grid = 2 * (int)std::min<int64_t>(n_pair, max_pairs);
+#else
+  const int grid = 2 * (int)((n_pair + waves - 1) / waves);
+#endif
   const float* P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   // tensor maps over the packed stage images of both nets: [2 * 39 * 256 rows x 64 bf16] (rows of 128 bytes, already
   // swizzled by the packer, so the map copies them verbatim); boxes of 128 rows (N = 256 layers) and 64 rows (view layer)

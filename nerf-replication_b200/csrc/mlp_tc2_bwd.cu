@@ -429,7 +429,14 @@ int mlp_tc2_dgrad(NerfEngine* h, int net, bool full, const RowSrc& src, const fl
   a.wpack = h->wpack_bwd + (size_t)(net == NERF_NET_FINE ? 1 : 0) * kNumStages * (kStageImage / 2);
   a.P = h->params + (net == NERF_NET_FINE ? NERF_PARAMS_PER_NET : 0);
   a.M = M; a.n_pair = (M + kRowsPerPair - 1) / kRowsPerPair;
-  const int grid = 2 * (int)std::min<int64_t>(a.n_pair, h->num_sms / 2);
+  // the fewest CTA pairs that keep the number of waves (1 024 training rays: 384 pair tiles = 6 waves on 74 pairs as on 64):
+  // every pair then runs the same number of tiles and the idle SMs give their power budget to the busy ones
+  const int64_t max_pairs = h->num_sms / 2, waves = (a.n_pair + max_pairs - 1) / max_pairs;
+#ifdef NERF_FULL_GRID      // A/B builds: every pair the device has
+  const int grid = 2 * (int)std::min<int64_t>(a.n_pair, max_pairs);
+#else
+  const int grid = 2 * (int)((a.n_pair + waves - 1) / waves);
+#endif
   if (full) mlp_tc2_dgrad_kernel<true><<<grid, kThreads, kSmemBytes, st>>>(a);
   else mlp_tc2_dgrad_kernel<false><<<grid, kThreads, kSmemBytes, st>>>(a);
   h->launches++;
