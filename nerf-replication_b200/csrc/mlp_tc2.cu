@@ -79,7 +79,7 @@ __host__ __device__ constexpr int sched_layer(int li) { return li < 8 ? li : (li
 __host__ __device__ constexpr uint32_t ring_slot_off(uint32_t slot) { return slot < kRingReal ? kOffW + slot * kHalfBytes : kOffPE + (slot - kRingReal) * kHalfBytes; }
 
 struct Bars {
-  uint64_t w_full[kRing], w_empty[kRing], b_full[kBiasRing], b_empty[kBiasRing], acc_full[2], act_ready[2];
+  uint64_t w_full[kRing], w_empty[kRing], b_full[kBiasRing], b_empty[kBiasRing], acc_full[2], act_ready[2], acc_free[2];
   uint32_t tmem_slot;
 };
 
@@ -284,6 +284,48 @@ __device__ __forceinline__ void tma_stage_cg2(void* smem_dst, const CUtensorMap*
 // activation arena straight from the epilogue registers (coalesced st.global.v4 in the arena's core-matrix order,
 // tc_arena.cuh), together with the ReLU bit masks the dgrad chain needs.  (Bulk shared->global stores of the same
 // blocks cost 40 % of the kernel: their shared-memory reads compete with the MMA operand fetch.)
+// NERF_TWO_PHASE (training forward): the epilogue first does what the render epilogue does -- accumulator -> ReLU -> bf16 ->
+// next layer's A operand -> hand-over -- and only then reads the SAME accumulator a second time to write the arena copy and
+// the ReLU bit masks.  In the per-tile order the issuer is busy with the other tile's MMAs for ~2 000 clk after a hand-over,
+// so the second pass (~1 300 clk of stores) was meant to leave the MMA -> epilogue -> MMA chain; a second barrier (acc_free)
+// keeps the issuer from overwriting an accumulator that is still being read.  Parity green, but SLOWER (forward 0.37 -> 0.43
+// ms, dgrad 0.34 -> 0.43 ms): the chain of ONE tile is  MMAs -> epilogue -> accumulator free -> MMAs, and with a single
+// accumulator per tile the second pass sits on it just like the stores did -- only now after a second TMEM read and a second
+// pack.  Kept as an option (default off).
+#ifndef NERF_TWO_PHASE
+#define NERF_TWO_PHASE 0      // measured: forward 0.37 -> 0.43 ms, dgrad 0.34 -> 0.43 ms (see the comment in mlp_tc2.cu / profiles/exp_train_r2.md)
+#endif
+// second pass of a trunk / feature layer: accumulator (bias included) -> (ReLU) -> bf16 -> this row of the arena blocks + mask record
+template <int MODE>
+__device__ __forceinline__ void epi_store_layer(uint32_t taddr, uint8_t* grow, uint8_t* gmask) {
+  uint32_t va[32], vb[32], mbits[8];
+  auto chunk = [&](const uint32_t (&v)[32], int c0) {
+    uint32_t pk[16];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float f0 = __uint_as_float(v[4 * j]), f1 = __uint_as_float(v[4 * j + 1]);
+      const float f2 = __uint_as_float(v[4 * j + 2]), f3 = __uint_as_float(v[4 * j + 3]);
+      if (MODE == 2) { pk[2 * j] = pack_bf16x2(f0, f1); pk[2 * j + 1] = pack_bf16x2(f2, f3); }
+      else { pk[2 * j] = pack_bf16x2_relu(f0, f1); pk[2 * j + 1] = pack_bf16x2_relu(f2, f3); }
+    }
+    uint8_t* gb = grow + (c0 >> 6) * 16384 + ((c0 & 63) >> 3) * 1024;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    if (MODE != 2) mbits[c0 >> 5] = pos_bits32(pk);
+  };
+  tmem_ld32(taddr, va);
+#pragma unroll
+  for (int c = 0; c < 8; c += 2) {
+    tmem_wait_ld();
+    tmem_ld32(taddr + (c + 1) * 32, vb);
+    chunk(va, c * 32);
+    tmem_wait_ld();
+    if (c + 2 < 8) tmem_ld32(taddr + (c + 2) * 32, va);
+    chunk(vb, (c + 1) * 32);
+  }
+  if (MODE != 2) st_global_mask8(gmask, mbits);
+}
+
 template <bool SAVE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64, int stage_row0, int n_rep,
@@ -296,6 +338,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
   }
   constexpr bool kPerTile = SAVE && !(NERF_EXP & 32);   // NERF_EXP bit 5: the saving forward in the render (shared-stage) order
   constexpr int kReps = kPerTile ? 2 : 1;            // weight passes per layer (training: once per tile, see the issuer)
+  constexpr bool kTwoPhase = SAVE && NERF_TWO_PHASE && !NERF_DEFER_STORES;
   Bars& sb = *reinterpret_cast<Bars*>(smem + kOffBar);
   float* s_walpha = reinterpret_cast<float*>(smem + kOffHeads);
   float* s_wrgb = s_walpha + 256;
@@ -308,7 +351,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
   if (tid == 0) {
     for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], 1); mbar_init(&sb.w_empty[i], 1); }   // w_full: used in the leader only
     for (int i = 0; i < kBiasRing; ++i) { mbar_init(&sb.b_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.b_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); mbar_init(&sb.acc_free[i], 8); }
     fence_barrier_init();
   }
   // constant A slab of the bias MMAs: 128 rows x 16 k bf16, un-swizzled K-major core matrices, columns 0..2 = 1.0
@@ -411,6 +454,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
 #pragma unroll
             for (int tile = 0; tile < 2; ++tile) {
               mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
+              if (kTwoPhase) mbar_wait(&sb.acc_free[tile], lc & 1u, 0x38 + tile);      // ... and its accumulator has been read twice
               tc_fence_after();
               if (lane == 0) trace_event(0x1000u | (tile << 8) | (li << 4) | 1u, 1024, tn, 0, 3000);
               {
@@ -443,6 +487,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
             mbar_wait(&sb.b_full[bslot], bpar, 0x28 + bslot);
             tc_fence_after();
             mbar_wait(&sb.act_ready[0], lc & 1u, 0x30);
+            if (kTwoPhase) mbar_wait(&sb.acc_free[0], lc & 1u, 0x38);
             tc_fence_after();
             issue_bias(0, bslot);
             for (int kb = 0; kb < nkb; ++kb, ++it) {
@@ -453,6 +498,7 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
               if (kb == nkb - 1) umma_commit2_w(&sb.acc_full[0], 0x3);
               if (kb == 0) {
                 mbar_wait(&sb.act_ready[1], lc & 1u, 0x31);
+                if (kTwoPhase) mbar_wait(&sb.acc_free[1], lc & 1u, 0x39);
                 tc_fence_after();
                 issue_bias(1, bslot);
                 umma_commit2_w(&sb.b_empty[bslot], 0x3);
@@ -488,6 +534,12 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
     };
+    const uint32_t free_addr = mapa_u32(smem_u32(&sb.acc_free[tile]), 0);
+    auto signal_free = [&]() {              // every tcgen05.ld of this warp on the tile's accumulator has completed
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(free_addr);
+    };
     uint32_t lc = 0, tn_e = 0;
     // this row of pair super-tile st_: validity, global row (through the compacted row list when rows are skipped), point, view direction
     auto row_setup = [&](int64_t st_, bool& valid_, int64_t& g_, float (&p_)[3], float (&vd_)[3]) {
@@ -514,9 +566,11 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
       auto gblk = [&](int slot) { return SAVE ? grow0 + (size_t)slot * arena::kBlockBytes : nullptr; };
       auto gmsk = [&](int layer) { return SAVE ? gmask0 + layer * arena::kMaskLayerBytes : nullptr; };
       constexpr bool kDefer = SAVE && NERF_DEFER_STORES;
-      store_pe_block(sPe, row_base, row_xor, pe, kDefer ? nullptr : gblk(arena::kActPE));
+      constexpr bool kLate = kDefer || kTwoPhase;       // arena copies of the PE blocks leave after the hand-over, from the registers
+      store_pe_block(sPe, row_base, row_xor, pe, kLate ? nullptr : gblk(arena::kActPE));
       signal_ready();
-      if (kDefer) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPE));      // from the registers, after the hand-over
+      if (kTwoPhase) signal_free();                      // the previous super-tile's last epilogue has drained the accumulator
+      if (kLate) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPE));
 
       float sigma = 0.f;
       bool nvalid = false;
@@ -537,16 +591,24 @@ mlp_tc2_forward_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_c
         if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 1u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
         if (li < 9) {
           uint8_t* grow = gblk(li < 8 ? arena::kActH + 4 * li : arena::kActFeat);
+          uint8_t* grow1 = kTwoPhase ? nullptr : grow;                                        // first pass: no arena stores
+          uint8_t* gmask1 = kTwoPhase ? nullptr : gmsk(arena::kMaskH + (li < 8 ? li : 0));
           uint32_t mbits[8];
-          if (li == 7) epi_layer<1>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li), mbits);
-          else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, nullptr, mbits);
-          else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow, gmsk(arena::kMaskH + li), mbits);
+          if (li == 7) epi_layer<1>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow1, gmask1, mbits);
+          else if (li == 8) epi_layer<2>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow1, nullptr, mbits);
+          else epi_layer<0>(taddr, s_walpha, sigma, sAct, row_base, row_xor, grow1, gmask1, mbits);
           // layer 5 has consumed PE(pts): the buffer now carries PE(dir) for the view branch
-          if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, kDefer ? nullptr : gblk(arena::kActPEDir));
+          if (li == 5) store_pe_block(sPe, row_base, row_xor, pe, kLate ? nullptr : gblk(arena::kActPEDir));
           if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 2u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
           signal_ready();
           if (tr) trace_event(0x2000u | (tile << 8) | (li << 4) | 3u, 1024, tn_e, 5000u + 1000u * tile, 6000u + 1000u * tile);
           if (SAVE) exp_bulk_rows_to_arena(sAct, q, lane, tile_base + (size_t)(li < 8 ? arena::kActH + 4 * li : arena::kActFeat) * arena::kBlockBytes, 4);
+          if (kTwoPhase) {     // second pass over the same accumulator: arena copy + ReLU bit masks, then release it
+            if (li == 8) epi_store_layer<2>(taddr, grow, nullptr);
+            else epi_store_layer<0>(taddr, grow, gmsk(arena::kMaskH + li));
+            signal_free();
+            if (li == 5) store_pe_block(nullptr, row_base, row_xor, pe, gblk(arena::kActPEDir));
+          }
           if (kDefer) {        // arena copy of this layer's output, its ReLU bit masks and (layer 5) PE(dir), off the critical path
             flush_row_to_arena(sAct, row_base, row_xor, grow, 4);
             if (li != 8) st_global_mask8(gmsk(arena::kMaskH + li), mbits);

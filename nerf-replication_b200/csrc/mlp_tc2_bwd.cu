@@ -32,7 +32,7 @@ constexpr uint32_t kOffBar = kOffHeads + (256 + 384) * 4;                       
 constexpr uint32_t kSmemBytes = kOffBar + 256;                                              // 232192 <= 232448
 
 struct Bars {
-  uint64_t w_full[kRing], w_empty[kRing], acc_full[2], act_ready[2];
+  uint64_t w_full[kRing], w_empty[kRing], acc_full[2], act_ready[2], acc_free[2];
   uint32_t tmem_slot;
 };
 static_assert(sizeof(Bars) <= 256, "barrier block");
@@ -63,12 +63,19 @@ __device__ __forceinline__ void sincos_turns(float x, float c_hi, float c_lo, fl
 #define NERF_DEFER_STORES 0
 #endif
 // 16 packed words (32 columns) -> shared-memory A operand (swizzled) [+ this row of the gradient arena block]
+// PASS 0: both; 1: A operand only (first pass of the two-phase epilogue); 2: arena only (second pass over the same accumulator)
+#ifndef NERF_TWO_PHASE
+#define NERF_TWO_PHASE 0      // measured: forward 0.37 -> 0.43 ms, dgrad 0.34 -> 0.43 ms (see the comment in mlp_tc2.cu / profiles/exp_train_r2.md)
+#endif
+template <int PASS = 0>
 __device__ __forceinline__ void put_chunk(const uint32_t (&pk)[16], int c0, uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint8_t* blk = sA + (c0 >> 6) * 16384;
   const int ch0 = (c0 & 63) >> 3;
+  if (PASS != 2) {
 #pragma unroll
-  for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-  if (!NERF_DEFER_STORES) {
+    for (int j = 0; j < 4; ++j) store_chunk(blk, row_base, row_xor, ch0 + j, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  }
+  if (!NERF_DEFER_STORES && PASS != 1) {
     uint8_t* gb = grow + (c0 >> 6) * 16384 + ch0 * 1024;
 #pragma unroll
     for (int j = 0; j < 4; ++j) st_global_cs(gb + j * 1024, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
@@ -91,7 +98,7 @@ __device__ __forceinline__ void flush_row_to_arena(const uint8_t* sA, uint32_t r
 
 // Epilogue of a masked step (F, L7..L1): 256 accumulator columns -> (+ d_sigma * w_alpha for F) -> bf16 -> AND
 // with the saved ReLU bit mask (mw: 8 words of this row) -> next A operand (in place) + gradient arena.
-template <bool ADD_ALPHA>
+template <bool ADD_ALPHA, int PASS = 0>
 __device__ __forceinline__ void epi_masked(uint32_t taddr, const uint32_t (&mw)[8], float dsigma, const float* __restrict__ s_walpha,
                                            uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint32_t va[32], vb[32];
@@ -108,7 +115,7 @@ __device__ __forceinline__ void epi_masked(uint32_t taddr, const uint32_t (&mw)[
       }
       pk[i] = pack_bf16x2(f0, f1) & mask2_from_bits(bits, i);
     }
-    put_chunk(pk, c0, sA, row_base, row_xor, grow);
+    put_chunk<PASS>(pk, c0, sA, row_base, row_xor, grow);
   };
   tmem_ld32(taddr, va);
 #pragma unroll
@@ -123,13 +130,14 @@ __device__ __forceinline__ void epi_masked(uint32_t taddr, const uint32_t (&mw)[
 }
 
 // Epilogue of the linear step V1 (d feature): 256 columns -> bf16 -> A operand + gradient arena.
+template <int PASS = 0>
 __device__ __forceinline__ void epi_linear(uint32_t taddr, uint8_t* sA, uint32_t row_base, uint32_t row_xor, uint8_t* grow) {
   uint32_t va[32], vb[32];
   auto chunk = [&](const uint32_t (&v)[32], int c0) {
     uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-    put_chunk(pk, c0, sA, row_base, row_xor, grow);
+    put_chunk<PASS>(pk, c0, sA, row_base, row_xor, grow);
   };
   tmem_ld32(taddr, va);
 #pragma unroll
@@ -155,6 +163,7 @@ struct DgradArgs {
   int64_t M, n_pair;
 };
 
+constexpr bool kTwoPhase = NERF_TWO_PHASE && !NERF_DEFER_STORES;
 template <bool FINE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2_dgrad_kernel(DgradArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -176,7 +185,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
   if ((smem_u32(smem) & 1023u) != 0) mbar_timeout(0xA13, smem_u32(smem));
   if (tid == 0) {
     for (int i = 0; i < kRing; ++i) { mbar_init(&sb.w_full[i], rank == 0 ? 2 : 1); mbar_init(&sb.w_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sb.acc_full[i], 1); mbar_init(&sb.act_ready[i], 8); mbar_init(&sb.acc_free[i], 8); }
     fence_barrier_init();
   }
   for (int i = tid; i < 256; i += kThreads) s_walpha[i] = __ldg(a.P + w_off(L_ALPHA) + i);
@@ -243,6 +252,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
 #pragma unroll
           for (int tile = 0; tile < 2; ++tile) {
             mbar_wait(&sb.act_ready[tile], lc & 1u, 0x30 + tile);
+            if (kTwoPhase) mbar_wait(&sb.acc_free[tile], lc & 1u, 0x38 + tile);      // the accumulator has been read twice (two-phase epilogue)
             tc_fence_after();
             for (int kb = 0; kb < nkb; ++kb, ++it) {
               const uint32_t slot = it % kRing, par = (it / kRing) & 1u;
@@ -271,6 +281,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(ready_addr);
+    };
+    const uint32_t free_addr = mapa_u32(smem_u32(&sb.acc_free[tile]), 0);
+    auto signal_free = [&]() {              // two-phase epilogue: every tcgen05.ld of this warp on the accumulator has completed
+      if (!kTwoPhase) return;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(free_addr);
     };
     uint32_t lc = 0;
     // ReLU bit masks of this row (saved by the forward; tc_arena.cuh).  The epilogues are the critical path of this kernel,
@@ -324,6 +341,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
         }
       }
       signal_ready();
+      signal_free();                          // the previous super-tile's last step has drained the accumulator
       flush_row_to_arena(sA, row_base, row_xor, grow0 + (size_t)(FINE ? arena::kGradHV : arena::kGradZ + 28) * arena::kBlockBytes, kInitBlocks);
 
       for (int i = 0; i < kSteps; ++i, ++lc) {
@@ -354,6 +372,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
             }
           }
           signal_ready();
+          signal_free();
         } else if (s == S_P0) {
           // d PE = dZ0 W0 + (layer-5 part) ; PE backward ; d t += d . d pts
           float dpe[64];
@@ -390,10 +409,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) mlp_tc2
           }
         } else {
           uint8_t* grow = grow0 + (size_t)step_out_slot(s) * arena::kBlockBytes;
-          if (s == S_V1) epi_linear(taddr, sA, row_base, row_xor, grow);
-          else if (s == S_F) epi_masked<true>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
-          else epi_masked<false>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
+          constexpr int kP1 = kTwoPhase ? 1 : 0;      // two-phase: A operand + hand-over first, the arena copy from a second read
+          if (s == S_V1) epi_linear<kP1>(taddr, sA, row_base, row_xor, grow);
+          else if (s == S_F) epi_masked<true, kP1>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
+          else epi_masked<false, kP1>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
           if (i + 1 < kSteps) signal_ready(); else tc_fence_before();
+          if (kTwoPhase) {
+            if (s == S_V1) epi_linear<2>(taddr, sA, row_base, row_xor, grow);
+            else if (s == S_F) epi_masked<true, 2>(taddr, mw_next, dr.w, s_walpha, sA, row_base, row_xor, grow);
+            else epi_masked<false, 2>(taddr, mw_next, 0.f, s_walpha, sA, row_base, row_xor, grow);
+            if (i + 1 < kSteps) signal_free(); else tc_fence_before();
+          }
           exp_bulk_rows_to_arena(sA, q, lane, a.grad_arena + (size_t)T * arena::grad_tile_bytes() + (size_t)step_out_slot(s) * arena::kBlockBytes, 4);
           flush_row_to_arena(sA, row_base, row_xor, grow, 4);
         }
